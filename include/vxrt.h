@@ -1,0 +1,165 @@
+/*
+ * vxrt.h — C ABI of the B200-native brickmap voxel ray tracer (libvxrt.so).
+ *
+ * This is the drop-in boundary for the reference's one hot path (JoshuaLim007/VoxelEngine,
+ * VoxelRT/): noise world build -> brickmap -> two-level DDA ray march -> shading.  The reference
+ * has no FFI layer; the calls below replace the C++ API that VoxelApp/main.cu uses, each entry
+ * citing the reference interface it stands in for (paths relative to the reference root).
+ * The header-compatible C++ shim with the reference's own names lives in include/voxelrt_compat/.
+ *
+ * Plain C: pointers and sizes only, no CUDA or torch types.  `stream` arguments are a
+ * cudaStream_t passed as void* (NULL = the legacy default stream).  Every function returns
+ * VX_OK (0) or a negative error; vx_last_error() gives the message of the calling thread's last
+ * failure.  There is no CPU fallback: without a CUDA device every compute entry fails with
+ * VX_ERR_CUDA.
+ */
+#ifndef VXRT_H
+#define VXRT_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VXRT_VERSION 100
+
+enum {
+    VX_OK = 0,
+    VX_ERR_INVALID = -1, /* bad argument (dims not multiples of factor, factor not a multiple of 8, ...) */
+    VX_ERR_CUDA = -2,    /* CUDA runtime error, message in vx_last_error() */
+    VX_ERR_CAPACITY = -3 /* more rays than the tracer was created for */
+};
+
+/* How Raytrace()'s `normalize(ray)` (helper_math.h:1325-1329) is evaluated.
+ * DEVICE: the device rsqrtf — what the reference's kernels do on a GPU (default).
+ * HOST:   (float)(1.0/sqrt((double)x)) — CUDA's host definition of rsqrtf
+ *         (crt/math_functions.hpp), i.e. what the reference computes when its source runs on a
+ *         CPU; used for bit-exact parity against the CPU oracle.
+ * NONE:   directions are taken as already normalised. */
+enum { VX_NORM_DEVICE = 0, VX_NORM_HOST = 1, VX_NORM_NONE = 2 };
+
+typedef struct vx_world vx_world;   /* brickmap resident on one GPU */
+typedef struct vx_tracer vx_tracer; /* per-device ray buffers bound to a world */
+
+const char* vx_last_error(void);
+int vx_version(void);
+int vx_device_count(int* count);
+
+/* ------------------------------------------------------------------------------------------
+ * World build.
+ * vx_world_build_noise replaces  CreateVoxels(uint3)                 VoxelWorldBuilder.cuh:12-32
+ *                              + GenerateLowresVoxelBuffer(buf, f)    VolumeRaytracer.cuh:379-516
+ *                              + VoxelRaytracer3D::Upload*            VolumeRaytracer.cu:527-572
+ * in one device-side pass (no dense host grid, no per-brick allocation).  (x0,y0,z0) selects a
+ * window of the infinite noise field (the reference always builds from 0,0,0).
+ * vx_world_from_dense_bits replaces GenerateLowresVoxelBuffer + Upload* for an externally
+ * supplied dense grid in the reference's tiled-linear bit layout (VolumeRaytracer.cuh:111-131).
+ * X,Y,Z must be multiples of `factor`, factor a multiple of 8, and X/factor, Y/factor, Z/factor
+ * multiples of 8 (the reference's coarse grid uses the same 8^3-tiled index).
+ * ------------------------------------------------------------------------------------------ */
+int vx_world_build_noise(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int factor,
+                         uint32_t x0, uint32_t y0, uint32_t z0, int device);
+int vx_world_from_dense_bits(vx_world** out, const uint32_t* host_tiled_bits, uint32_t X, uint32_t Y,
+                             uint32_t Z, int factor, int device);
+int vx_world_destroy(vx_world* w);
+/* Diagnostics: same as vx_world_build_noise with the exact early-out of the noise evaluation
+ * disabled (every voxel runs all 32 octaves, as the reference's PopulateVoxels does). */
+int vx_world_build_noise_full(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int factor,
+                              uint32_t x0, uint32_t y0, uint32_t z0, int device);
+
+typedef struct vx_world_info {
+    uint32_t dims[3];        /* voxels */
+    uint32_t coarse[3];      /* bricks */
+    int32_t factor;
+    int32_t device;
+    uint64_t bricks;          /* coarse cells */
+    uint64_t occupied_bricks; /* bricks with at least one voxel (= slots in the pool) */
+    uint64_t solid_voxels;
+    uint64_t bytes_top, bytes_records, bytes_pool;
+    float build_ms;           /* device time of the last build (CUDA events) */
+} vx_world_info;
+int vx_world_get_info(const vx_world* w, vx_world_info* info);
+
+/* Reference-form export for parity checks: coarse occupancy bits (tiled index, (bricks+31)/32
+ * words), per-brick masks indexed by coarse tiled index (bricks * factor^3/32 words, zeros for
+ * empty bricks) and per-brick bounds (bricks * 6 floats: min xyz, max xyz; 0,0,0,-1,-1,-1 when
+ * empty) — exactly what GenerateLowresVoxelBuffer returns.  Any pointer may be NULL. */
+int vx_world_download(const vx_world* w, uint32_t* top_words, uint32_t* brick_words, float* bounds6);
+
+/* ------------------------------------------------------------------------------------------
+ * Tracer.  Replaces VoxelRaytracer3D(size_t count) / ~VoxelRaytracer3D  VolumeRaytracer.cuh:318-334
+ * ------------------------------------------------------------------------------------------ */
+int vx_tracer_create(vx_tracer** out, vx_world* w, size_t max_rays);
+int vx_tracer_destroy(vx_tracer* t);
+
+/* Per-ray result planes (structure of arrays).  Any pointer may be NULL.
+ * hit/pos/normal/steps are what the reference's `dispatch` kernel returns
+ * (VolumeRaytracer.cu:95-117: pos = +inf on a miss, normal un-negated); the rest are the locals
+ * of Raytrace() the parity contract compares. */
+typedef struct vx_hits {
+    uint8_t* hit;          /* n */
+    float* pos;            /* n*3 */
+    float* normal;         /* n*3 */
+    int32_t* steps;        /* n */
+    int32_t* voxel;        /* n*3: coarse cell*factor + fine cell, -1 on a miss */
+    uint32_t* brick;       /* n: tiled coarse index (VolumeRaytracer.cu:419), 0xFFFFFFFF on a miss */
+    int32_t* coarse_steps; /* n */
+    int32_t* fine_steps;   /* n */
+    uint32_t* counters;    /* n*3: C coarse cells examined, K occupied cells examined, E bricks entered */
+} vx_hits;
+
+typedef struct vx_trace_opts {
+    int32_t norm_mode; /* VX_NORM_* */
+    int32_t max_steps; /* Raytrace(maxSteps, ...); 0 = MAX_STEPS = 2048 (VolumeRaytracer.cuh:235) */
+} vx_trace_opts;
+
+/* Batch rays, host buffers: H2D of origins/dirs, kernel, D2H of the requested planes.
+ * Replaces RayTraceResults<float3> VoxelRaytracer3D::Raytrace(vector<float3>, vector<float3>)
+ * (VolumeRaytracer.cu:574-618).  opts may be NULL (defaults). */
+int vx_trace(vx_tracer* t, const float* origins_xyz, const float* dirs_xyz, size_t n,
+             const vx_trace_opts* opts, const vx_hits* out_host);
+/* Same, all pointers are device pointers on the tracer's device; asynchronous on `stream`. */
+int vx_trace_device(vx_tracer* t, const float* d_origins_xyz, const float* d_dirs_xyz, size_t n,
+                    const vx_trace_opts* opts, const vx_hits* out_dev, void* stream);
+/* Host post-processing of the batch API (VolumeRaytracer.cu:601-614): valid / distance. */
+int vx_hits_postprocess(const float* origins_xyz, const float* pos, size_t n, uint8_t* valid, float* distance);
+
+/* ------------------------------------------------------------------------------------------
+ * Screen render.  Replaces Graphics::RenderScreen (Renderer.cu:305-328) and the process globals
+ * behind SetEnvironment / SetFOV (Renderer.cu:278-303), which are passed explicitly here.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct vx_camera {
+    float origin[3], fwd[3], up[3], right[3]; /* as produced by Graphics::GetDirections */
+    float fov_deg;                            /* SetFOV */
+    float tan_half;                           /* 0: tanf(fov/2) evaluated on the device as the reference does */
+} vx_camera;
+typedef struct vx_env { float light_dir[3], light_color[3], ambient[3]; } vx_env; /* Renderer.cuh:33-37 */
+typedef struct vx_render_opts {
+    int32_t checkerboard;  /* 1 = reference (ENABLE_CHECKERBOARD_RENDER, Renderer.cu:5) */
+    uint32_t frame_number; /* dFrameInfo.FrameNumber during the frame */
+    int32_t debug_view;    /* 1 = shipped DEBUG_VIEW quadrants (Renderer.cu:4,215-243,270-275) */
+    int32_t shadows;       /* 1 = sun shadow ray of Renderer.cu:102 enabled */
+    int32_t crosshair;     /* 1 = reference (Renderer.cu:260-268) */
+    int32_t norm_mode;     /* VX_NORM_* */
+    uint32_t tile_x0, tile_y0, tile_w, tile_h; /* thread-space rectangle to render; w=h=0: whole frame */
+} vx_render_opts;
+
+void vx_get_directions(const float euler_xyz[3], float fwd[3], float up[3], float right[3]); /* Renderer.cu:27-42 */
+/* d_bgra: W*H*4 bytes of device memory, BGRA8888 (Renderer.cuh:29-31); asynchronous on `stream`.
+ * d_steps (optional, W*H int32): per-pixel step count incl. shadow steps. */
+int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* opts,
+              void* d_bgra, int32_t* d_steps, uint32_t W, uint32_t H, void* stream);
+/* Same into host memory (render into the tracer's device frame, then D2H; synchronous): the
+ * RenderScreen + cudaMemcpy pair of VoxelApp/main.cu:165-167. */
+int vx_render_host(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* opts,
+                   void* h_bgra, uint32_t W, uint32_t H);
+
+/* Device math the parity harness shares with the CPU oracle. */
+int vx_device_tanf(float x, float* out, int device);
+int vx_device_normalize(const float* dirs_xyz, float* out_xyz, size_t n, int device); /* device rsqrtf */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,81 @@
+// vx_host.h — host-side objects behind the C ABI (include/vxrt.h) and error plumbing.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include "../../include/vxrt.h"
+#include "vx_device.cuh"
+
+namespace vx {
+
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define VX_CUDA(call)                                                                   \
+    do {                                                                                \
+        cudaError_t vx_e_ = (call);                                                     \
+        if (vx_e_ != cudaSuccess) return vx::cuda_fail(vx_e_, #call, __FILE__, __LINE__); \
+    } while (0)
+
+#define VX_REQUIRE(cond, msg)                 \
+    do {                                      \
+        if (!(cond)) {                        \
+            vx::set_error(msg);               \
+            return VX_ERR_INVALID;            \
+        }                                     \
+    } while (0)
+
+// Restores the caller's current device on scope exit.
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int device) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        ok = cudaSetDevice(device) == cudaSuccess;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+} // namespace vx
+
+struct vx_world {
+    int device = 0;
+    uint32_t X = 0, Y = 0, Z = 0;
+    int factor = 8;
+    uint32_t cx = 0, cy = 0, cz = 0;
+    uint64_t nbricks = 0, occupied = 0, solid_voxels = 0;
+    uint32_t words_per_brick = 16;
+    uint32_t* d_top = nullptr;   // (nbricks+31)/32 words
+    uint2* d_records = nullptr;  // nbricks
+    uint32_t* d_pool = nullptr;  // occupied * words_per_brick
+    float build_ms = 0.0f;
+    vx::WorldView view() const {
+        vx::WorldView v;
+        v.top = d_top; v.records = d_records; v.pool = d_pool;
+        v.cx = (int)cx; v.cy = (int)cy; v.cz = (int)cz; v.factor = factor;
+        v.words_per_brick = words_per_brick; v.tiles_x = cx / 8; v.tiles_xy = (cx / 8) * (cy / 8);
+        return v;
+    }
+};
+
+struct vx_tracer {
+    vx_world* world = nullptr;
+    int device = 0;
+    size_t max_rays = 0;
+    // staging for the host-buffer entry points
+    float* d_origins = nullptr;
+    float* d_dirs = nullptr;
+    uint8_t* d_hit = nullptr;
+    float* d_pos = nullptr;
+    float* d_normal = nullptr;
+    int32_t* d_steps = nullptr;
+    int32_t* d_voxel = nullptr;
+    uint32_t* d_brick = nullptr;
+    int32_t* d_csteps = nullptr;
+    int32_t* d_fsteps = nullptr;
+    uint32_t* d_counters = nullptr;
+    void* d_frame = nullptr; size_t frame_bytes = 0; // vx_render_host
+    float tan_arg = -1.0f, tan_val = 0.0f;           // cached device tanf
+    cudaStream_t stream = nullptr;
+};

@@ -1,0 +1,353 @@
+// vx_trace.cu — batch ray kernel, screen render kernel and their C ABI.
+//
+// Replaces the reference's `dispatch` kernel + VoxelRaytracer3D::Raytrace (VolumeRaytracer.cu:95-117,
+// :574-618) and `screenDispatch` + Graphics::RenderScreen (Renderer.cu:179-328).  The march itself
+// is vx_device.cuh.  Ray-to-thread mapping, launch shapes and buffers are new.
+#include "vx_host.h"
+
+namespace vx {
+
+struct HitPlanes {
+    uint8_t* hit; float* pos; float* normal; int32_t* steps; int32_t* voxel; uint32_t* brick;
+    int32_t* coarse_steps; int32_t* fine_steps; uint32_t* counters;
+};
+
+template <int NORM, bool COUNT>
+__global__ void __launch_bounds__(128) trace_rays(WorldView w, const float* __restrict__ origins, const float* __restrict__ dirs,
+                                                  size_t n, int max_steps, HitPlanes out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V3 o = mk(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]);
+    const V3 d = mk(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
+    MarchOut m;
+    const bool h = march<NORM, COUNT>(w, o, d, max_steps, m);
+    if (out.hit) out.hit[i] = h;
+    if (out.pos) {
+        out.pos[3 * i] = h ? m.pos.x : CUDART_INF_F; out.pos[3 * i + 1] = h ? m.pos.y : CUDART_INF_F; out.pos[3 * i + 2] = h ? m.pos.z : CUDART_INF_F;
+    }
+    if (out.normal) { out.normal[3 * i] = m.normal.x; out.normal[3 * i + 1] = m.normal.y; out.normal[3 * i + 2] = m.normal.z; }
+    if (out.steps) out.steps[i] = m.steps;
+    if (out.voxel) { out.voxel[3 * i] = m.voxel[0]; out.voxel[3 * i + 1] = m.voxel[1]; out.voxel[3 * i + 2] = m.voxel[2]; }
+    if (out.brick) out.brick[i] = m.brick;
+    if (out.coarse_steps) out.coarse_steps[i] = m.coarse_steps;
+    if (out.fine_steps) out.fine_steps[i] = m.fine_steps;
+    if (COUNT && out.counters) { out.counters[3 * i] = m.work.C; out.counters[3 * i + 1] = m.work.K; out.counters[3 * i + 2] = m.work.E; }
+}
+
+// ---- screen ----------------------------------------------------------------------------------
+struct FrameParams {
+    V3 origin, fwd, up, right;
+    V3 light, light_color, ambient;
+    float tan_half;
+    uint32_t W, H;
+    uint32_t frame_number;
+    int checkerboard, debug_view, shadows, crosshair;
+    uint32_t tx0, ty0, tw, th; // thread-space rectangle
+};
+
+__device__ __forceinline__ void put_pixel(uint8_t* __restrict__ bgra, uint32_t W, uint32_t H, int x, int y, V3 c) {
+    // setPixelColor, Renderer.cu:72-87: clamp, float->uint8 truncation, B,G,R,A byte order
+    if ((uint32_t)x >= W || (uint32_t)y >= H) return;
+    c.x = fminf(fmaxf(c.x, 0.0f), 1.0f); c.y = fminf(fmaxf(c.y, 0.0f), 1.0f); c.z = fminf(fmaxf(c.z, 0.0f), 1.0f);
+    const uint32_t r = (uint32_t)(int)fmul(c.x, 255.0f), g = (uint32_t)(int)fmul(c.y, 255.0f), b = (uint32_t)(int)fmul(c.z, 255.0f);
+    reinterpret_cast<uint32_t*>(bgra)[(size_t)y * W + x] = b | (g << 8) | (r << 16) | 0xFF000000u;
+}
+
+template <int NORM>
+__device__ __forceinline__ V3 shade(const WorldView& w, const FrameParams& f, V3 n, V3 pos, int& extra_steps) {
+    // calculateColor, Renderer.cu:90-168 (AO block: samples = 0, no-op)
+    extra_steps = 0;
+    const V3 sray = normalize3<NORM>(f.light);
+    const V3 spos = mk(fadd(pos.x, fmul(sray.x, 0.01f)), fadd(pos.y, fmul(sray.y, 0.01f)), fadd(pos.z, fmul(sray.z, 0.01f)));
+    bool shadowed = false;
+    if (f.shadows) {
+        MarchOut m;
+        shadowed = march<NORM, false>(w, spos, sray, kMaxSteps, m);
+        extra_steps += m.steps;
+    }
+    const float nl = dot3(n, f.light);
+    const float ldot = fmul(fmaxf(nl, 0.0f), shadowed ? 0.0f : 1.0f);
+    const float up_dot = dot3(n, mk(0.0f, 1.0f, 0.0f));
+    const float t = (float)__dadd_rn(__dmul_rn((double)up_dot, 0.5), 0.5); // double expression, Renderer.cu:106
+    const float amb = fadd(0.25f, fmul(t, 0.75f));                          // helper_math lerp(0.25, 1.0, t)
+    V3 c = mk(fadd(fmul(ldot, f.light_color.x), fmul(f.ambient.x, amb)), fadd(fmul(ldot, f.light_color.y), fmul(f.ambient.y, amb)),
+              fadd(fmul(ldot, f.light_color.z), fmul(f.ambient.z, amb)));
+    if (!shadowed) {
+        const V3 view = normalize3<NORM>(mk(fsub(pos.x, f.origin.x), fsub(pos.y, f.origin.y), fsub(pos.z, f.origin.z)));
+        const V3 refl = mk(fsub(f.light.x, fmul(fmul(2.0f, n.x), nl)), fsub(f.light.y, fmul(fmul(2.0f, n.y), nl)),
+                           fsub(f.light.z, fmul(fmul(2.0f, n.z), nl)));
+        const float spec = powf(fmaxf(dot3(view, refl), 0.0f), 32.0f);
+        c = mk(fadd(c.x, fmul(spec, f.light_color.x)), fadd(c.y, fmul(spec, f.light_color.y)), fadd(c.z, fmul(spec, f.light_color.z)));
+    }
+    return c;
+}
+
+// One thread per reference thread coordinate (tx,ty); a warp covers an 8x4 block of thread
+// coordinates instead of the reference's 32x1 strip (coherence), results are identical.
+template <int NORM>
+__global__ void __launch_bounds__(128) render_frame(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    // block = 4 warps = 16x8 thread coordinates; warp = 8x4
+    const uint32_t tx = f.tx0 + blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
+    const uint32_t ty = f.ty0 + blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+    if (tx >= f.tx0 + f.tw || ty >= f.ty0 + f.th) return;
+    int x = (int)tx, y = (int)ty;
+    if (f.checkerboard) { // Renderer.cu:186-194
+        y *= 2;
+        if ((x % 2) == 0) y += 1;
+        if (f.frame_number % 2u == 0u) y += 1;
+    }
+    if ((uint32_t)x >= f.W || (uint32_t)y >= f.H) return;
+    const int W = (int)f.W, H = (int)f.H;
+    // getRayDirection, Renderer.cu:44-59
+    const float u = fsub(fmul(fdiv((float)x, (float)W), 2.0f), 1.0f), v = fsub(fmul(fdiv((float)y, (float)H), 2.0f), 1.0f);
+    const float aspect = fdiv((float)W, (float)H);
+    const float a = fmul(u, fmul(f.tan_half, aspect)), b = fmul(v, f.tan_half);
+    V3 rd = mk(fadd(fadd(f.fwd.x, fmul(a, f.right.x)), fmul(b, f.up.x)), fadd(fadd(f.fwd.y, fmul(a, f.right.y)), fmul(b, f.up.y)),
+               fadd(fadd(f.fwd.z, fmul(a, f.right.z)), fmul(b, f.up.z)));
+    rd = normalize3<NORM>(rd);
+    MarchOut m;
+    const bool hit = march<NORM, false>(w, f.origin, rd, kMaxSteps, m);
+    int steps = m.steps;
+    const V3 n = mk(-m.normal.x, -m.normal.y, -m.normal.z);
+    if (hit) {
+        if (f.debug_view) { // Renderer.cu:215-243
+            const V3 dl = mk(fsub(m.pos.x, f.origin.x), fsub(m.pos.y, f.origin.y), fsub(m.pos.z, f.origin.z));
+            const float dist = __fsqrt_rn(dot3(dl, dl));
+            const float md = (float)(1.0 + kEpsDDA);
+            const V3 hp = mk(fmodf(fdiv(m.pos.x, 128.0f), md), fmodf(fdiv(m.pos.y, 128.0f), md), fmodf(fdiv(m.pos.z, 128.0f), md));
+            if (x < (W >> 1) && y < (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, n);
+            else if (x >= (W >> 1) && y < (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, hp);
+            else if (x < (W >> 1)) {}
+            else put_pixel(bgra, f.W, f.H, x, y, mk(fmul(dist, 0.01f), 0.0f, 0.0f));
+        } else {
+            int extra = 0;
+            V3 c = shade<NORM>(w, f, n, m.pos, extra);
+            c = mk(fdiv(c.x, fadd(c.x, 1.0f)), fdiv(c.y, fadd(c.y, 1.0f)), fdiv(c.z, fadd(c.z, 1.0f))); // Tonemap, Renderer.cu:170-177
+            steps += extra;
+            put_pixel(bgra, f.W, f.H, x, y, c);
+        }
+    } else {
+        put_pixel(bgra, f.W, f.H, x, y, rd); // Renderer.cu:254-258
+    }
+    if (f.crosshair && tx == (f.W >> 1) && ty == (f.H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(10.0f, 10.0f, 10.0f));
+    if (f.debug_view && x < (W >> 1) && y > (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(fdiv((float)steps, 256.0f), 0.0f, 0.0f));
+    if (steps_plane) steps_plane[(size_t)y * f.W + x] = steps;
+}
+
+__global__ void tanf_kernel(float x, float* out) { *out = tanf(x); }
+__global__ void normalize_kernel(const float* __restrict__ in, float* __restrict__ out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V3 v = normalize3<0>(mk(in[3 * i], in[3 * i + 1], in[3 * i + 2]));
+    out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
+}
+
+} // namespace vx
+
+// =============================================================================================
+// host side
+// =============================================================================================
+using namespace vx;
+
+extern "C" int vx_tracer_create(vx_tracer** out, vx_world* w, size_t max_rays) {
+    VX_REQUIRE(out && w, "NULL argument");
+    *out = nullptr;
+    DeviceGuard guard(w->device);
+    if (!guard.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+    vx_tracer* t = new vx_tracer();
+    t->world = w; t->device = w->device; t->max_rays = max_rays;
+    const size_t n = max_rays ? max_rays : 1;
+#define VX_ALLOC(ptr, bytes) do { cudaError_t e_ = cudaMalloc((void**)&(ptr), (bytes)); if (e_ != cudaSuccess) { vx_tracer_destroy(t); return cuda_fail(e_, "cudaMalloc", __FILE__, __LINE__); } } while (0)
+    VX_ALLOC(t->d_origins, n * 12); VX_ALLOC(t->d_dirs, n * 12);
+    VX_ALLOC(t->d_hit, n); VX_ALLOC(t->d_pos, n * 12); VX_ALLOC(t->d_normal, n * 12); VX_ALLOC(t->d_steps, n * 4);
+    VX_ALLOC(t->d_voxel, n * 12); VX_ALLOC(t->d_brick, n * 4); VX_ALLOC(t->d_csteps, n * 4); VX_ALLOC(t->d_fsteps, n * 4);
+    VX_ALLOC(t->d_counters, n * 12);
+#undef VX_ALLOC
+    VX_CUDA(cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking));
+    *out = t;
+    return VX_OK;
+}
+
+extern "C" int vx_tracer_destroy(vx_tracer* t) {
+    if (!t) return VX_OK;
+    DeviceGuard guard(t->device);
+    cudaFree(t->d_origins); cudaFree(t->d_dirs); cudaFree(t->d_hit); cudaFree(t->d_pos); cudaFree(t->d_normal);
+    cudaFree(t->d_steps); cudaFree(t->d_voxel); cudaFree(t->d_brick); cudaFree(t->d_csteps); cudaFree(t->d_fsteps);
+    cudaFree(t->d_counters); cudaFree(t->d_frame);
+    if (t->stream) cudaStreamDestroy(t->stream);
+    delete t;
+    return VX_OK;
+}
+
+static int launch_trace(vx_tracer* t, const float* d_o, const float* d_d, size_t n, const vx_trace_opts* opts, const vx_hits* out,
+                        cudaStream_t s) {
+    if (n == 0) return VX_OK;
+    const int norm = opts ? opts->norm_mode : VX_NORM_DEVICE;
+    const int max_steps = (opts && opts->max_steps > 0) ? opts->max_steps : kMaxSteps;
+    VX_REQUIRE(norm >= 0 && norm <= 2, "bad norm_mode");
+    HitPlanes p{out->hit, out->pos, out->normal, out->steps, out->voxel, out->brick, out->coarse_steps, out->fine_steps, out->counters};
+    const WorldView w = t->world->view();
+    const unsigned blocks = (unsigned)((n + 127) / 128);
+    const bool count = out->counters != nullptr;
+#define VX_LAUNCH(N, C) trace_rays<N, C><<<blocks, 128, 0, s>>>(w, d_o, d_d, n, max_steps, p)
+    if (count) { if (norm == 0) VX_LAUNCH(0, true); else if (norm == 1) VX_LAUNCH(1, true); else VX_LAUNCH(2, true); }
+    else { if (norm == 0) VX_LAUNCH(0, false); else if (norm == 1) VX_LAUNCH(1, false); else VX_LAUNCH(2, false); }
+#undef VX_LAUNCH
+    VX_CUDA(cudaGetLastError());
+    return VX_OK;
+}
+
+extern "C" int vx_trace_device(vx_tracer* t, const float* d_origins, const float* d_dirs, size_t n, const vx_trace_opts* opts,
+                               const vx_hits* out_dev, void* stream) {
+    VX_REQUIRE(t && out_dev && (n == 0 || (d_origins && d_dirs)), "NULL argument");
+    DeviceGuard guard(t->device);
+    return launch_trace(t, d_origins, d_dirs, n, opts, out_dev, (cudaStream_t)stream);
+}
+
+extern "C" int vx_trace(vx_tracer* t, const float* origins, const float* dirs, size_t n, const vx_trace_opts* opts, const vx_hits* out) {
+    VX_REQUIRE(t && out && (n == 0 || (origins && dirs)), "NULL argument");
+    if (n > t->max_rays) { set_error("vx_trace: more rays than the tracer was created for"); return VX_ERR_CAPACITY; }
+    if (n == 0) return VX_OK;
+    DeviceGuard guard(t->device);
+    cudaStream_t s = t->stream;
+    VX_CUDA(cudaMemcpyAsync(t->d_origins, origins, n * 12, cudaMemcpyHostToDevice, s));
+    VX_CUDA(cudaMemcpyAsync(t->d_dirs, dirs, n * 12, cudaMemcpyHostToDevice, s));
+    vx_hits dev;
+    dev.hit = out->hit ? t->d_hit : nullptr; dev.pos = out->pos ? t->d_pos : nullptr; dev.normal = out->normal ? t->d_normal : nullptr;
+    dev.steps = out->steps ? t->d_steps : nullptr; dev.voxel = out->voxel ? t->d_voxel : nullptr; dev.brick = out->brick ? t->d_brick : nullptr;
+    dev.coarse_steps = out->coarse_steps ? t->d_csteps : nullptr; dev.fine_steps = out->fine_steps ? t->d_fsteps : nullptr;
+    dev.counters = out->counters ? t->d_counters : nullptr;
+    int rc = launch_trace(t, t->d_origins, t->d_dirs, n, opts, &dev, s);
+    if (rc) return rc;
+#define VX_BACK(h, d, bytes) if (h) VX_CUDA(cudaMemcpyAsync(h, d, (bytes), cudaMemcpyDeviceToHost, s))
+    VX_BACK(out->hit, t->d_hit, n); VX_BACK(out->pos, t->d_pos, n * 12); VX_BACK(out->normal, t->d_normal, n * 12);
+    VX_BACK(out->steps, t->d_steps, n * 4); VX_BACK(out->voxel, t->d_voxel, n * 12); VX_BACK(out->brick, t->d_brick, n * 4);
+    VX_BACK(out->coarse_steps, t->d_csteps, n * 4); VX_BACK(out->fine_steps, t->d_fsteps, n * 4); VX_BACK(out->counters, t->d_counters, n * 12);
+#undef VX_BACK
+    VX_CUDA(cudaStreamSynchronize(s));
+    return VX_OK;
+}
+
+extern "C" int vx_hits_postprocess(const float* origins, const float* pos, size_t n, uint8_t* valid, float* distance) {
+    // VolumeRaytracer.cu:601-614; distance is computed for misses too (inf), as the reference does
+    VX_REQUIRE(origins && pos, "NULL argument");
+    for (size_t i = 0; i < n; ++i) {
+        const float inf = __builtin_inff();
+        if (valid) valid[i] = pos[3 * i] != inf && pos[3 * i + 1] != inf && pos[3 * i + 2] != inf;
+        if (distance) {
+            const float dx = origins[3 * i] - pos[3 * i], dy = origins[3 * i + 1] - pos[3 * i + 1], dz = origins[3 * i + 2] - pos[3 * i + 2];
+            distance[i] = __builtin_sqrtf(dx * dx + dy * dy + dz * dz);
+        }
+    }
+    return VX_OK;
+}
+
+extern "C" void vx_get_directions(const float e[3], float fwd[3], float up[3], float right[3]) {
+    // Graphics::GetDirections, Renderer.cu:27-42 (host path: float overloads of cos/sin)
+    const float cxr = __builtin_cosf(e[0]), sxr = __builtin_sinf(e[0]), cyr = __builtin_cosf(e[1]), syr = __builtin_sinf(e[1]);
+    const float fx = cxr * syr, fy = -sxr, fz = cxr * cyr;
+    const float rx = cyr, ry = 0.0f, rz = -syr;
+    const float ux = fy * rz - fz * ry, uy = fz * rx - fx * rz, uz = fx * ry - fy * rx;
+    fwd[0] = fx * -1.0f; fwd[1] = fy * -1.0f; fwd[2] = fz * -1.0f;
+    up[0] = ux * -1.0f; up[1] = uy * -1.0f; up[2] = uz * -1.0f;
+    right[0] = rx; right[1] = ry; right[2] = rz;
+}
+
+extern "C" int vx_device_tanf(float x, float* out, int device) {
+    VX_REQUIRE(out != nullptr, "out is NULL");
+    DeviceGuard guard(device);
+    float* d = nullptr;
+    VX_CUDA(cudaMalloc(&d, 4));
+    tanf_kernel<<<1, 1>>>(x, d);
+    cudaError_t e = cudaMemcpy(out, d, 4, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    VX_CUDA(e);
+    return VX_OK;
+}
+
+extern "C" int vx_device_normalize(const float* dirs, float* out, size_t n, int device) {
+    VX_REQUIRE(dirs && out, "NULL argument");
+    if (!n) return VX_OK;
+    DeviceGuard guard(device);
+    float *di = nullptr, *d_out = nullptr;
+    VX_CUDA(cudaMalloc(&di, n * 12));
+    VX_CUDA(cudaMalloc(&d_out, n * 12));
+    VX_CUDA(cudaMemcpy(di, dirs, n * 12, cudaMemcpyHostToDevice));
+    normalize_kernel<<<(unsigned)((n + 255) / 256), 256>>>(di, d_out, n);
+    cudaError_t e = cudaMemcpy(out, d_out, n * 12, cudaMemcpyDeviceToHost);
+    cudaFree(di); cudaFree(d_out);
+    VX_CUDA(e);
+    return VX_OK;
+}
+
+static int fill_frame(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* o, uint32_t W, uint32_t H, FrameParams& f) {
+    VX_REQUIRE(W > 0 && H > 0, "empty frame");
+    f.origin = V3{cam->origin[0], cam->origin[1], cam->origin[2]};
+    f.fwd = V3{cam->fwd[0], cam->fwd[1], cam->fwd[2]};
+    f.up = V3{cam->up[0], cam->up[1], cam->up[2]};
+    f.right = V3{cam->right[0], cam->right[1], cam->right[2]};
+    f.light = V3{env->light_dir[0], env->light_dir[1], env->light_dir[2]};
+    f.light_color = V3{env->light_color[0], env->light_color[1], env->light_color[2]};
+    f.ambient = V3{env->ambient[0], env->ambient[1], env->ambient[2]};
+    if (cam->tan_half > 0.0f) f.tan_half = cam->tan_half;
+    else {
+        // float fov = FOV * 3.1415 / 180.0; tanf(fov / 2.0f) — Renderer.cu:50-52, evaluated on the device once
+        const float fov = (float)((double)cam->fov_deg * 3.1415 / 180.0);
+        const float arg = fov / 2.0f;
+        if (t->tan_arg != arg) {
+            int rc = vx_device_tanf(arg, &t->tan_val, t->device);
+            if (rc) return rc;
+            t->tan_arg = arg;
+        }
+        f.tan_half = t->tan_val;
+    }
+    f.W = W; f.H = H;
+    f.frame_number = o->frame_number;
+    f.checkerboard = o->checkerboard; f.debug_view = o->debug_view; f.shadows = o->shadows; f.crosshair = o->crosshair;
+    const uint32_t rows = o->checkerboard ? (H >> 1) : H; // RenderScreen, Renderer.cu:311-316
+    const uint32_t cols = (W + 31u) / 32u * 32u;
+    if (o->tile_w && o->tile_h) {
+        f.tx0 = o->tile_x0; f.ty0 = o->tile_y0;
+        f.tw = o->tile_x0 < cols ? (o->tile_w < cols - o->tile_x0 ? o->tile_w : cols - o->tile_x0) : 0;
+        f.th = o->tile_y0 < rows ? (o->tile_h < rows - o->tile_y0 ? o->tile_h : rows - o->tile_y0) : 0;
+    } else { f.tx0 = 0; f.ty0 = 0; f.tw = cols; f.th = rows; }
+    return VX_OK;
+}
+
+extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* opts, void* d_bgra, int32_t* d_steps,
+                         uint32_t W, uint32_t H, void* stream) {
+    VX_REQUIRE(t && cam && env && opts && d_bgra, "NULL argument");
+    VX_REQUIRE(opts->norm_mode == VX_NORM_DEVICE || opts->norm_mode == VX_NORM_HOST, "render supports VX_NORM_DEVICE or VX_NORM_HOST");
+    DeviceGuard guard(t->device);
+    FrameParams f;
+    int rc = fill_frame(t, cam, env, opts, W, H, f);
+    if (rc) return rc;
+    if (f.tw == 0 || f.th == 0) return VX_OK;
+    const dim3 grid((f.tw + 15u) / 16u, (f.th + 7u) / 8u);
+    const WorldView w = t->world->view();
+    if (opts->norm_mode == VX_NORM_HOST) render_frame<1><<<grid, 128, 0, (cudaStream_t)stream>>>(w, f, (uint8_t*)d_bgra, d_steps);
+    else render_frame<0><<<grid, 128, 0, (cudaStream_t)stream>>>(w, f, (uint8_t*)d_bgra, d_steps);
+    VX_CUDA(cudaGetLastError());
+    return VX_OK;
+}
+
+extern "C" int vx_render_host(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* opts, void* h_bgra, uint32_t W,
+                              uint32_t H) {
+    VX_REQUIRE(t && h_bgra, "NULL argument");
+    DeviceGuard guard(t->device);
+    const size_t bytes = (size_t)W * H * 4;
+    if (t->frame_bytes < bytes) {
+        cudaFree(t->d_frame); t->d_frame = nullptr; t->frame_bytes = 0;
+        VX_CUDA(cudaMalloc(&t->d_frame, bytes));
+        t->frame_bytes = bytes;
+        // first use: seed the device frame with the caller's buffer so that unwritten pixels
+        // (checkerboard, debug bottom-left) keep their previous value, as in the reference
+        VX_CUDA(cudaMemcpyAsync(t->d_frame, h_bgra, bytes, cudaMemcpyHostToDevice, t->stream));
+    }
+    int rc = vx_render(t, cam, env, opts, t->d_frame, nullptr, W, H, t->stream);
+    if (rc) return rc;
+    VX_CUDA(cudaMemcpyAsync(h_bgra, t->d_frame, bytes, cudaMemcpyDeviceToHost, t->stream));
+    VX_CUDA(cudaStreamSynchronize(t->stream));
+    return VX_OK;
+}

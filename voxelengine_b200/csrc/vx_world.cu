@@ -1,0 +1,426 @@
+// vx_world.cu — brickmap construction on the device.
+//
+// Replaces the reference's start-up chain: PopulateVoxels kernel + dense D2H copy
+// (VoxelWorldBuilder.cuh:12-32), the host-thread GenerateLowresVoxelBuffer (VolumeRaytracer.cuh:379-516)
+// and the per-brick cudaMalloc uploads (VolumeRaytracer.cu:527-572) by four kernels:
+//   A  noise_tiles / dense_tiles : one warp per 8^3 tile, ballot-assembled 512-bit masks
+//   B  analyse_bricks            : occupancy, packed tight bounds, voxel count (one warp per brick)
+//   C  scan (3 small kernels)    : exclusive prefix over occupancy -> pool slot
+//   D  compact_bricks            : copy occupied bricks into the compact pool
+// Layout: DESIGN.md §2.
+#include "vx_host.h"
+#include "vx_noise.cuh"
+
+namespace vx {
+
+// ---- brick/tile enumeration ---------------------------------------------------------------
+// Global tile id t = brick * tiles_per_brick + sub, brick = reference tiled coarse index.
+struct BuildGeom {
+    uint32_t cx, cy, cz;     // coarse dims
+    uint32_t f8;             // factor / 8
+    uint32_t tpb;            // tiles per brick = f8^3
+    uint32_t x0, y0, z0;     // noise window origin
+    uint32_t X, Y;           // voxel dims (dense source)
+};
+__device__ __forceinline__ void brick_coords(uint32_t brick, const BuildGeom& g, uint32_t& bx, uint32_t& by, uint32_t& bz) {
+    // inverse of the tiled index, VolumeRaytracer.cuh:143-163
+    const uint32_t tW = g.cx >> 3, tH = g.cy >> 3;
+    const uint32_t tile = brick >> 9, fine = brick & 511u;
+    bx = (tile % tW) * 8u + (fine & 7u);
+    by = ((tile / tW) % tH) * 8u + ((fine >> 3) & 7u);
+    bz = (tile / (tW * tH)) * 8u + (fine >> 6);
+}
+
+// ---- A1: noise -> tile masks ----------------------------------------------------------------
+// One warp per 8^3 tile.  Lane l owns the 16 voxels {i*32 + l}; a flattened (voxel, octave) loop
+// keeps the warp converged while lanes sit in different octaves (early-out, vx_noise.cuh).
+template <bool EARLY_OUT>
+__global__ void __launch_bounds__(256) noise_tiles(uint32_t* __restrict__ tmp, BuildGeom g, uint64_t ntiles) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    for (uint64_t t = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < ntiles; t += warps) {
+        const uint32_t brick = (uint32_t)(t / g.tpb), sub = (uint32_t)(t % g.tpb);
+        uint32_t bx, by, bz;
+        brick_coords(brick, g, bx, by, bz);
+        const uint32_t f = g.f8 * 8u;
+        const int vx0 = (int)(g.x0 + bx * f + (sub % g.f8) * 8u + (lane & 7u));
+        const int vy0 = (int)(g.y0 + by * f + ((sub / g.f8) % g.f8) * 8u + (lane >> 3));
+        const int vz0 = (int)(g.z0 + bz * f + (sub / (g.f8 * g.f8)) * 8u);
+        uint32_t bits = 0; // bit i = voxel i*32+lane: y = vy0 + 4*(i&1), z = vz0 + (i>>1)
+        int i = 0;
+        Terrain tr;
+        tr.begin(vx0, vy0, vz0);
+        while (i < 16) {
+            tr.octave();
+            int dec;
+            if (EARLY_OUT) dec = tr.decided();
+            else dec = tr.k >= kOctaves ? tr.decided() : -1;
+            if (dec >= 0) {
+                bits |= (uint32_t)dec << i;
+                ++i;
+                tr.begin(vx0, vy0 + ((i & 1) << 2), vz0 + (i >> 1));
+            }
+        }
+        uint32_t mine = 0;
+#pragma unroll
+        for (int w = 0; w < 16; ++w) {
+            const uint32_t word = __ballot_sync(0xFFFFFFFFu, (bits >> w) & 1u);
+            if (lane == (uint32_t)w) mine = word;
+        }
+        if (lane < 16u) tmp[t * 16u + lane] = mine;
+    }
+}
+
+// ---- A2: external dense grid (reference tiled layout) -> tile masks --------------------------
+__global__ void __launch_bounds__(256) dense_tiles(uint32_t* __restrict__ tmp, const uint32_t* __restrict__ dense, BuildGeom g,
+                                                   uint64_t ntiles) {
+    const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; // one thread per 32-bit word
+    if (gid >= ntiles * 16u) return;
+    const uint64_t t = gid >> 4;
+    const uint32_t wd = (uint32_t)gid & 15u;
+    const uint32_t brick = (uint32_t)(t / g.tpb), sub = (uint32_t)(t % g.tpb);
+    uint32_t bx, by, bz;
+    brick_coords(brick, g, bx, by, bz);
+    const uint64_t tx = (uint64_t)bx * g.f8 + sub % g.f8, ty = (uint64_t)by * g.f8 + (sub / g.f8) % g.f8,
+                   tz = (uint64_t)bz * g.f8 + sub / (g.f8 * g.f8);
+    const uint64_t src_tile = tx + ty * (g.X >> 3) + tz * (uint64_t)(g.X >> 3) * (g.Y >> 3);
+    tmp[gid] = dense[src_tile * 16u + wd];
+}
+
+// ---- B: per-brick occupancy, bounds, count --------------------------------------------------
+// Word wd of a tile holds voxels z = wd>>1, y = 4*(wd&1)..+3, one byte per y row, bit = x.
+__global__ void __launch_bounds__(256) analyse_bricks(const uint32_t* __restrict__ tmp, uint2* __restrict__ records,
+                                                      uint32_t* __restrict__ top, unsigned long long* __restrict__ solid,
+                                                      BuildGeom g, uint32_t nbricks) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t brick = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (brick >= nbricks) return;
+    const uint32_t words = g.tpb * 16u;
+    int mnx = 255, mny = 255, mnz = 255, mxx = -1, mxy = -1, mxz = -1;
+    uint32_t count = 0;
+    for (uint32_t wi = lane; wi < words; wi += 32u) {
+        const uint32_t v = tmp[(uint64_t)brick * words + wi];
+        if (!v) continue;
+        count += __popc(v);
+        const uint32_t sub = wi >> 4, wd = wi & 15u;
+        const int ox = (int)((sub % g.f8) * 8u), oy = (int)(((sub / g.f8) % g.f8) * 8u + ((wd & 1u) << 2)),
+                  oz = (int)((sub / (g.f8 * g.f8)) * 8u + (wd >> 1));
+        const uint32_t xm = (v | (v >> 8) | (v >> 16) | (v >> 24)) & 255u;
+        const uint32_t ym = ((v & 0xFFu) ? 1u : 0u) | ((v & 0xFF00u) ? 2u : 0u) | ((v & 0xFF0000u) ? 4u : 0u) | ((v & 0xFF000000u) ? 8u : 0u);
+        mnx = min(mnx, ox + (__ffs(xm) - 1)); mxx = max(mxx, ox + (31 - __clz(xm)));
+        mny = min(mny, oy + (__ffs(ym) - 1)); mxy = max(mxy, oy + (31 - __clz(ym)));
+        mnz = min(mnz, oz); mxz = max(mxz, oz);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mnx = min(mnx, __shfl_xor_sync(0xFFFFFFFFu, mnx, o)); mxx = max(mxx, __shfl_xor_sync(0xFFFFFFFFu, mxx, o));
+        mny = min(mny, __shfl_xor_sync(0xFFFFFFFFu, mny, o)); mxy = max(mxy, __shfl_xor_sync(0xFFFFFFFFu, mxy, o));
+        mnz = min(mnz, __shfl_xor_sync(0xFFFFFFFFu, mnz, o)); mxz = max(mxz, __shfl_xor_sync(0xFFFFFFFFu, mxz, o));
+        count += __shfl_xor_sync(0xFFFFFFFFu, count, o);
+    }
+    if (lane == 0) {
+        uint32_t packed = 0;
+        if (count) {
+            packed = (uint32_t)mnx | ((uint32_t)mny << 5) | ((uint32_t)mnz << 10) | ((uint32_t)mxx << 15) | ((uint32_t)mxy << 20) |
+                     ((uint32_t)mxz << 25);
+            atomicOr(&top[brick >> 5], 1u << (brick & 31u));
+            atomicAdd(solid, (unsigned long long)count);
+        }
+        records[brick] = make_uint2(packed, 0xFFFFFFFFu);
+    }
+}
+
+// ---- C: exclusive scan of the occupancy bits (popcount per word) ----------------------------
+constexpr int kScanBlock = 1024; // words per block
+__global__ void __launch_bounds__(kScanBlock) scan_block_sums(const uint32_t* __restrict__ top, uint32_t nwords, uint32_t* __restrict__ block_sums) {
+    __shared__ uint32_t warp_sums[32];
+    const uint32_t i = blockIdx.x * kScanBlock + threadIdx.x;
+    uint32_t v = i < nwords ? __popc(top[i]) : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        uint32_t s = warp_sums[threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+        if (threadIdx.x == 0) block_sums[blockIdx.x] = s;
+    }
+}
+__global__ void scan_block_offsets(uint32_t* __restrict__ block_sums, uint32_t nblocks, unsigned long long* __restrict__ total) {
+    // single thread block; nblocks is small (2048 at 8k x 512 x 8k)
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < nblocks; base += blockDim.x) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < nblocks ? block_sums[i] : 0u;
+        // Hillis-Steele inclusive scan in shared memory
+        __shared__ uint32_t buf[1024];
+        buf[threadIdx.x] = v;
+        __syncthreads();
+        for (uint32_t o = 1; o < blockDim.x; o <<= 1) {
+            const uint32_t add = threadIdx.x >= o ? buf[threadIdx.x - o] : 0u;
+            __syncthreads();
+            buf[threadIdx.x] += add;
+            __syncthreads();
+        }
+        if (i < nblocks) block_sums[i] = carry + buf[threadIdx.x] - v;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry += buf[threadIdx.x];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = carry;
+}
+__global__ void __launch_bounds__(kScanBlock) scan_assign_slots(const uint32_t* __restrict__ top, uint32_t nwords,
+                                                                const uint32_t* __restrict__ block_offsets, uint2* __restrict__ records) {
+    __shared__ uint32_t warp_sums[32];
+    const uint32_t i = blockIdx.x * kScanBlock + threadIdx.x;
+    const uint32_t word = i < nwords ? top[i] : 0u;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t incl = __popc(word);
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= (uint32_t)o) incl += n;
+    }
+    if (lane == 31u) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t s = warp_sums[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, s, o);
+            if (lane >= (uint32_t)o) s += n;
+        }
+        warp_sums[lane] = s; // inclusive over warps
+    }
+    __syncthreads();
+    uint32_t base = block_offsets[blockIdx.x] + (warp ? warp_sums[warp - 1] : 0u) + incl - __popc(word);
+    uint32_t m = word;
+    while (m) {
+        const uint32_t b = __ffs(m) - 1;
+        m &= m - 1;
+        records[(uint64_t)i * 32u + b].y = base++;
+    }
+}
+
+// ---- D: compaction ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) compact_bricks(const uint32_t* __restrict__ tmp, const uint2* __restrict__ records,
+                                                      uint32_t* __restrict__ pool, uint32_t words, uint64_t total_words) {
+    // one thread per 16-byte chunk
+    const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid * 4u >= total_words) return;
+    const uint32_t brick = (uint32_t)((gid * 4u) / words);
+    const uint32_t off = (uint32_t)((gid * 4u) % words);
+    const uint32_t slot = records[brick].y;
+    if (slot == 0xFFFFFFFFu) return;
+    const uint4 v = *reinterpret_cast<const uint4*>(tmp + (uint64_t)brick * words + off);
+    *reinterpret_cast<uint4*>(pool + (uint64_t)slot * words + off) = v;
+}
+
+// ---- export (parity) -------------------------------------------------------------------------
+__global__ void export_bricks(const uint2* __restrict__ records, const uint32_t* __restrict__ top, const uint32_t* __restrict__ pool,
+                              uint32_t words, uint32_t nbricks, uint32_t* __restrict__ brick_words, float* __restrict__ bounds6) {
+    const uint32_t brick = blockIdx.x;
+    if (brick >= nbricks) return;
+    const bool occ = (top[brick >> 5] >> (brick & 31u)) & 1u;
+    const uint2 rec = records[brick];
+    if (brick_words)
+        for (uint32_t i = threadIdx.x; i < words; i += blockDim.x)
+            brick_words[(uint64_t)brick * words + i] = occ ? pool[(uint64_t)rec.y * words + i] : 0u;
+    if (bounds6 && threadIdx.x == 0) {
+        float* o = bounds6 + (uint64_t)brick * 6u;
+        if (occ) {
+            const uint32_t b = rec.x;
+            o[0] = (float)(b & 31u); o[1] = (float)((b >> 5) & 31u); o[2] = (float)((b >> 10) & 31u);
+            o[3] = (float)((b >> 15) & 31u); o[4] = (float)((b >> 20) & 31u); o[5] = (float)((b >> 25) & 31u);
+        } else {
+            o[0] = o[1] = o[2] = 0.0f; o[3] = o[4] = o[5] = -1.0f;
+        }
+    }
+}
+
+} // namespace vx
+
+// =============================================================================================
+// host side
+// =============================================================================================
+namespace vx {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+    char buf[512];
+    snprintf(buf, sizeof buf, "CUDA error %d (%s) in %s at %s:%d", (int)e, cudaGetErrorString(e), what, file, line);
+    g_last_error = buf;
+    cudaGetLastError(); // clear the sticky-less error state
+    return VX_ERR_CUDA;
+}
+
+static int check_dims(uint32_t X, uint32_t Y, uint32_t Z, int factor) {
+    VX_REQUIRE(factor >= 8 && factor <= 32 && factor % 8 == 0, "factor must be 8, 16, 24 or 32");
+    VX_REQUIRE(X && Y && Z && X % factor == 0 && Y % factor == 0 && Z % factor == 0, "X, Y, Z must be non-zero multiples of factor");
+    VX_REQUIRE((X / factor) % 8 == 0 && (Y / factor) % 8 == 0 && (Z / factor) % 8 == 0,
+               "X/factor, Y/factor, Z/factor must be multiples of 8 (reference tiled coarse index)");
+    VX_REQUIRE(X / factor <= 65535 && Y / factor <= 65535 && Z / factor <= 65535, "coarse dimensions exceed uint16 (reference VoxelBuffer)");
+    VX_REQUIRE((uint64_t)(X / factor) * (Y / factor) * (Z / factor) < (1ull << 32) / 1, "too many bricks for a 32-bit brick index");
+    return VX_OK;
+}
+
+// Runs stages B-D on `d_tmp` (all tiles, brick-major) and fills `w`.
+static int finish_build(vx_world* w, const uint32_t* d_tmp, const BuildGeom& g) {
+    const uint32_t nb = (uint32_t)w->nbricks;
+    const uint32_t words = w->words_per_brick;
+    const uint32_t nwords_top = (nb + 31) / 32;
+    unsigned long long* d_counters = nullptr; // [0] solid voxels, [1] occupied bricks
+    uint32_t* d_block_sums = nullptr;
+    VX_CUDA(cudaMalloc(&w->d_top, (size_t)nwords_top * 4));
+    VX_CUDA(cudaMemset(w->d_top, 0, (size_t)nwords_top * 4));
+    VX_CUDA(cudaMalloc(&w->d_records, (size_t)nb * sizeof(uint2)));
+    VX_CUDA(cudaMalloc(&d_counters, 16));
+    VX_CUDA(cudaMemset(d_counters, 0, 16));
+    analyse_bricks<<<(uint32_t)(((uint64_t)nb * 32 + 255) / 256), 256>>>(d_tmp, w->d_records, w->d_top, d_counters, g, nb);
+    VX_CUDA(cudaGetLastError());
+    const uint32_t nblocks = (nwords_top + kScanBlock - 1) / kScanBlock;
+    VX_CUDA(cudaMalloc(&d_block_sums, (size_t)nblocks * 4));
+    scan_block_sums<<<nblocks, kScanBlock>>>(w->d_top, nwords_top, d_block_sums);
+    scan_block_offsets<<<1, 1024>>>(d_block_sums, nblocks, d_counters + 1);
+    scan_assign_slots<<<nblocks, kScanBlock>>>(w->d_top, nwords_top, d_block_sums, w->d_records);
+    VX_CUDA(cudaGetLastError());
+    unsigned long long h[2] = {0, 0};
+    VX_CUDA(cudaMemcpy(h, d_counters, 16, cudaMemcpyDeviceToHost));
+    w->solid_voxels = h[0];
+    w->occupied = h[1];
+    const size_t pool_words = (size_t)(w->occupied ? w->occupied : 1) * words;
+    VX_CUDA(cudaMalloc(&w->d_pool, pool_words * 4));
+    const uint64_t total_words = (uint64_t)nb * words;
+    compact_bricks<<<(uint32_t)((total_words / 4 + 255) / 256), 256>>>(d_tmp, w->d_records, w->d_pool, words, total_words);
+    VX_CUDA(cudaGetLastError());
+    VX_CUDA(cudaDeviceSynchronize());
+    cudaFree(d_counters);
+    cudaFree(d_block_sums);
+    return VX_OK;
+}
+
+static void free_world(vx_world* w) {
+    if (!w) return;
+    cudaFree(w->d_top); cudaFree(w->d_records); cudaFree(w->d_pool);
+    delete w;
+}
+
+static int build_common(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int factor, uint32_t x0, uint32_t y0, uint32_t z0,
+                        int device, const uint32_t* host_dense, uint32_t flags) {
+    VX_REQUIRE(out != nullptr, "out is NULL");
+    *out = nullptr;
+    int rc = check_dims(X, Y, Z, factor);
+    if (rc) return rc;
+    VX_REQUIRE((uint64_t)x0 + X < (1ull << 31) && (uint64_t)y0 + Y < (1ull << 31) && (uint64_t)z0 + Z < (1ull << 31), "window exceeds int range");
+    DeviceGuard guard(device);
+    if (!guard.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+    vx_world* w = new vx_world();
+    w->device = device; w->X = X; w->Y = Y; w->Z = Z; w->factor = factor;
+    w->cx = X / factor; w->cy = Y / factor; w->cz = Z / factor;
+    w->nbricks = (uint64_t)w->cx * w->cy * w->cz;
+    w->words_per_brick = (uint32_t)factor * factor * factor / 32;
+    BuildGeom g;
+    g.cx = w->cx; g.cy = w->cy; g.cz = w->cz; g.f8 = factor / 8; g.tpb = g.f8 * g.f8 * g.f8;
+    g.x0 = x0; g.y0 = y0; g.z0 = z0; g.X = X; g.Y = Y;
+    const uint64_t ntiles = w->nbricks * g.tpb;
+    uint32_t* d_tmp = nullptr;
+    uint32_t* d_dense = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    auto cleanup = [&]() { cudaFree(d_tmp); cudaFree(d_dense); if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); };
+#define VX_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); free_world(w); return cuda_fail(e_, #call, __FILE__, __LINE__); } } while (0)
+    VX_TRY(cudaMalloc(&d_tmp, (size_t)ntiles * 64));
+    VX_TRY(cudaEventCreate(&e0));
+    VX_TRY(cudaEventCreate(&e1));
+    if (host_dense) {
+        VX_TRY(cudaMalloc(&d_dense, (size_t)ntiles * 64));
+        VX_TRY(cudaMemcpy(d_dense, host_dense, (size_t)ntiles * 64, cudaMemcpyHostToDevice));
+    }
+    VX_TRY(cudaEventRecord(e0));
+    if (host_dense) {
+        dense_tiles<<<(uint32_t)((ntiles * 16 + 255) / 256), 256>>>(d_tmp, d_dense, g, ntiles);
+    } else {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        const uint64_t want = (ntiles + 7) / 8; // 8 warps per block
+        const uint32_t blocks = (uint32_t)(want < (uint64_t)sms * 64 ? want : (uint64_t)sms * 64);
+        if (flags & 1u) noise_tiles<false><<<blocks, 256>>>(d_tmp, g, ntiles);
+        else noise_tiles<true><<<blocks, 256>>>(d_tmp, g, ntiles);
+    }
+    VX_TRY(cudaGetLastError());
+    rc = finish_build(w, d_tmp, g);
+    if (rc) { cleanup(); free_world(w); return rc; }
+    VX_TRY(cudaEventRecord(e1));
+    VX_TRY(cudaEventSynchronize(e1));
+    VX_TRY(cudaEventElapsedTime(&w->build_ms, e0, e1));
+#undef VX_TRY
+    cleanup();
+    *out = w;
+    return VX_OK;
+}
+
+} // namespace vx
+
+using namespace vx;
+
+extern "C" const char* vx_last_error(void) { return g_last_error.c_str(); }
+extern "C" int vx_version(void) { return VXRT_VERSION; }
+extern "C" int vx_device_count(int* count) {
+    VX_REQUIRE(count != nullptr, "count is NULL");
+    *count = 0;
+    VX_CUDA(cudaGetDeviceCount(count));
+    return VX_OK;
+}
+
+extern "C" int vx_world_build_noise(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int factor, uint32_t x0, uint32_t y0,
+                                    uint32_t z0, int device) {
+    return build_common(out, X, Y, Z, factor, x0, y0, z0, device, nullptr, 0u);
+}
+// Validation build: every voxel runs all 32 octaves (no early-out).  Not in vxrt.h's main surface;
+// declared there under "diagnostics".
+extern "C" int vx_world_build_noise_full(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int factor, uint32_t x0, uint32_t y0,
+                                         uint32_t z0, int device) {
+    return build_common(out, X, Y, Z, factor, x0, y0, z0, device, nullptr, 1u);
+}
+extern "C" int vx_world_from_dense_bits(vx_world** out, const uint32_t* host_tiled_bits, uint32_t X, uint32_t Y, uint32_t Z, int factor,
+                                        int device) {
+    VX_REQUIRE(host_tiled_bits != nullptr, "host_tiled_bits is NULL");
+    return build_common(out, X, Y, Z, factor, 0, 0, 0, device, host_tiled_bits, 0u);
+}
+extern "C" int vx_world_destroy(vx_world* w) {
+    if (!w) return VX_OK;
+    DeviceGuard guard(w->device);
+    free_world(w);
+    return VX_OK;
+}
+extern "C" int vx_world_get_info(const vx_world* w, vx_world_info* info) {
+    VX_REQUIRE(w && info, "NULL argument");
+    info->dims[0] = w->X; info->dims[1] = w->Y; info->dims[2] = w->Z;
+    info->coarse[0] = w->cx; info->coarse[1] = w->cy; info->coarse[2] = w->cz;
+    info->factor = w->factor; info->device = w->device;
+    info->bricks = w->nbricks; info->occupied_bricks = w->occupied; info->solid_voxels = w->solid_voxels;
+    info->bytes_top = (w->nbricks + 31) / 32 * 4; info->bytes_records = w->nbricks * 8;
+    info->bytes_pool = w->occupied * w->words_per_brick * 4;
+    info->build_ms = w->build_ms;
+    return VX_OK;
+}
+extern "C" int vx_world_download(const vx_world* w, uint32_t* top_words, uint32_t* brick_words, float* bounds6) {
+    VX_REQUIRE(w != nullptr, "world is NULL");
+    DeviceGuard guard(w->device);
+    const uint32_t nb = (uint32_t)w->nbricks;
+    if (top_words) VX_CUDA(cudaMemcpy(top_words, w->d_top, (size_t)((nb + 31) / 32) * 4, cudaMemcpyDeviceToHost));
+    if (brick_words || bounds6) {
+        uint32_t* d_bw = nullptr; float* d_b6 = nullptr;
+        if (brick_words) VX_CUDA(cudaMalloc(&d_bw, (size_t)nb * w->words_per_brick * 4));
+        if (bounds6) VX_CUDA(cudaMalloc(&d_b6, (size_t)nb * 24));
+        export_bricks<<<nb, 32>>>(w->d_records, w->d_top, w->d_pool, w->words_per_brick, nb, d_bw, d_b6);
+        VX_CUDA(cudaGetLastError());
+        if (brick_words) VX_CUDA(cudaMemcpy(brick_words, d_bw, (size_t)nb * w->words_per_brick * 4, cudaMemcpyDeviceToHost));
+        if (bounds6) VX_CUDA(cudaMemcpy(bounds6, d_b6, (size_t)nb * 24, cudaMemcpyDeviceToHost));
+        cudaFree(d_bw); cudaFree(d_b6);
+    }
+    return VX_OK;
+}
