@@ -143,6 +143,9 @@ typedef struct vx_render_opts {
     int32_t crosshair;     /* 1 = reference (Renderer.cu:260-268) */
     int32_t norm_mode;     /* VX_NORM_* */
     uint32_t tile_x0, tile_y0, tile_w, tile_h; /* thread-space rectangle to render; w=h=0: whole frame */
+    uint64_t* d_stats;     /* optional DEVICE pointer to 8 counters the frame adds to: primary rays, primary
+                              hits, shadow rays, shadow hits, steps, C, K, E (work counters of vx_hits);
+                              the counting variant of the kernel is slower — leave NULL when timing */
 } vx_render_opts;
 
 void vx_get_directions(const float euler_xyz[3], float fwd[3], float up[3], float right[3]); /* Renderer.cu:27-42 */
@@ -158,6 +161,9 @@ int vx_render_host(vx_tracer* t, const vx_camera* cam, const vx_env* env, const 
 /* Device math the parity harness shares with the CPU oracle. */
 int vx_device_tanf(float x, float* out, int device);
 int vx_device_normalize(const float* dirs_xyz, float* out_xyz, size_t n, int device); /* device rsqrtf */
+/* Diagnostics: best-of-4 streaming read rate of a `bytes`-sized buffer read `reps` times by every SM
+ * (ld.global.cg, 16 B per thread): the L2 roofline denominator when bytes << L2, HBM when bytes >> L2. */
+int vx_measure_read_bandwidth(int device, size_t bytes, int reps, float* gb_per_s);
 
 #ifdef __cplusplus
 }

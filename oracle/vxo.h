@@ -49,6 +49,9 @@ void vxo_populate_dense(uint32_t* bits, uint32_t X, uint32_t Y, uint32_t Z,
 /* ---- brickmap (VolumeRaytracer.cuh:379-516) ---- */
 vxo_world* vxo_world_from_dense(const uint32_t* tiled_bits, uint32_t X, uint32_t Y, uint32_t Z, int factor);
 vxo_world* vxo_world_from_noise(uint32_t X, uint32_t Y, uint32_t Z, int factor, int f2u_mode, int nthreads);
+/* non-owning view of an existing reference-form brickmap (no dense grid): for the timed CPU baseline */
+vxo_world* vxo_world_from_brickmap_view(const uint32_t* top_bits, const uint32_t* brick_bits, const float* bounds6,
+                                        uint32_t X, uint32_t Y, uint32_t Z, int factor);
 void vxo_world_free(vxo_world* w);
 void vxo_world_dims(const vxo_world* w, uint32_t dims_xyz[3], uint32_t coarse_xyz[3], int* factor);
 const uint32_t* vxo_world_dense_bits(const vxo_world* w);   /* X*Y*Z bits, tiled index */

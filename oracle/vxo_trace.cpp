@@ -120,7 +120,7 @@ void dda(const Level& L, V3 s, V3 d, const float* bounds6, int scale, int clip_m
 bool march(const vxo_world& w, V3 origin, V3 ray, int norm_mode, int max_steps, MarchOut& o) {
     const int f = w.factor;
     const float ff = (float)f;
-    Level top{w.top.data(), (int)w.cx, (int)w.cy, (int)w.cz};
+    Level top{w.top_p, (int)w.cx, (int)w.cy, (int)w.cz};
     float prev[3] = {-1, -1, -1};
     int total = 0;
     o = MarchOut{};
@@ -140,7 +140,7 @@ bool march(const vxo_world& w, V3 origin, V3 ray, int norm_mode, int max_steps, 
     bool hit = false;
     while (total < max_steps) {
         DdaOut c;
-        dda(top, start, d, w.bounds.data(), f, -1, c, &o.work);
+        dda(top, start, d, w.bounds_p, f, -1, c, &o.work);
         total += c.steps; o.coarse_steps += c.steps;
         V3 local{c.point.x * ff, c.point.y * ff, c.point.z * ff};
         hit_pos = local;
@@ -151,7 +151,7 @@ bool march(const vxo_world& w, V3 origin, V3 ray, int norm_mode, int max_steps, 
         const float bx = hc[0] * ff, by = hc[1] * ff, bz = hc[2] * ff;
         local.x -= bx; local.y -= by; local.z -= bz;
         const uint64_t bi = sample_index((uint32_t)c.cell[0], (uint32_t)c.cell[1], (uint32_t)c.cell[2], w.cx, w.cy);
-        Level brick{w.brick_bits.data() + bi * w.words_per_brick, f, f, f};
+        Level brick{w.brick_p + bi * w.words_per_brick, f, f, f};
         o.work.E++;
         DdaOut q;
         dda(brick, local, d, nullptr, 0, f, q, nullptr);
@@ -256,10 +256,10 @@ extern "C" void vxo_dda(const vxo_world* w, int level, uint32_t brick_index, con
     DdaOut r;
     V3 S{s[0], s[1], s[2]}, D{d[0], d[1], d[2]};
     if (level == 0) {
-        Level top{w->top.data(), (int)w->cx, (int)w->cy, (int)w->cz};
-        dda(top, S, D, w->bounds.data(), w->factor, -1, r, nullptr);
+        Level top{w->top_p, (int)w->cx, (int)w->cy, (int)w->cz};
+        dda(top, S, D, w->bounds_p, w->factor, -1, r, nullptr);
     } else {
-        Level brick{w->brick_bits.data() + (size_t)brick_index * w->words_per_brick, w->factor, w->factor, w->factor};
+        Level brick{w->brick_p + (size_t)brick_index * w->words_per_brick, w->factor, w->factor, w->factor};
         dda(brick, S, D, nullptr, 0, w->factor, r, nullptr);
     }
     flags[0] = r.hit; flags[1] = r.oob; *steps = r.steps;

@@ -179,6 +179,21 @@ static void build_bricks(vxo_world* w, int nthreads) {
     });
     w->top.assign((nb + 31) / 32, 0u);
     for (size_t i = 0; i < nb; ++i) if (any[i]) bit_set(w->top.data(), i);
+    w->bind();
+}
+
+/* Adopt a brickmap that already exists in the reference's form (e.g. downloaded from the GPU build
+ * for the timed CPU baseline at sizes the CPU cannot generate): no copy, the caller keeps the
+ * arrays alive.  There is no dense grid in such a world. */
+extern "C" vxo_world* vxo_world_from_brickmap_view(const uint32_t* top, const uint32_t* brick_bits, const float* bounds6,
+                                                   uint32_t X, uint32_t Y, uint32_t Z, int factor) {
+    if (factor < 8 || factor % 8 || X % factor || Y % factor || Z % factor) return nullptr;
+    vxo_world* w = new vxo_world();
+    w->X = X; w->Y = Y; w->Z = Z; w->factor = factor;
+    w->cx = X / factor; w->cy = Y / factor; w->cz = Z / factor;
+    w->words_per_brick = (size_t)factor * factor * factor / 32;
+    w->top_p = top; w->brick_p = brick_bits; w->bounds_p = bounds6;
+    return w;
 }
 
 extern "C" vxo_world* vxo_world_from_dense(const uint32_t* bits, uint32_t X, uint32_t Y, uint32_t Z, int factor) {
@@ -210,6 +225,6 @@ extern "C" void vxo_world_dims(const vxo_world* w, uint32_t d[3], uint32_t c[3],
     d[0] = w->X; d[1] = w->Y; d[2] = w->Z; c[0] = w->cx; c[1] = w->cy; c[2] = w->cz; *factor = w->factor;
 }
 extern "C" const uint32_t* vxo_world_dense_bits(const vxo_world* w) { return w->dense.data(); }
-extern "C" const uint32_t* vxo_world_top_bits(const vxo_world* w) { return w->top.data(); }
-extern "C" const uint32_t* vxo_world_brick_bits(const vxo_world* w) { return w->brick_bits.data(); }
-extern "C" const float* vxo_world_bounds(const vxo_world* w) { return w->bounds.data(); }
+extern "C" const uint32_t* vxo_world_top_bits(const vxo_world* w) { return w->top_p; }
+extern "C" const uint32_t* vxo_world_brick_bits(const vxo_world* w) { return w->brick_p; }
+extern "C" const float* vxo_world_bounds(const vxo_world* w) { return w->bounds_p; }

@@ -13,5 +13,10 @@ struct vxo_world {
     std::vector<uint32_t> top;        /* coarse occupancy bits, tiled index over (cx,cy,cz) */
     std::vector<uint32_t> brick_bits; /* per brick factor^3 bits, in-brick tiled index */
     std::vector<float> bounds;        /* per brick min xyz, max xyz (inclusive voxel coords) */
+    /* what the march reads: the vectors above, or caller-owned arrays (vxo_world_from_brickmap_view) */
+    const uint32_t* top_p = nullptr;
+    const uint32_t* brick_p = nullptr;
+    const float* bounds_p = nullptr;
+    void bind() { top_p = top.data(); brick_p = brick_bits.data(); bounds_p = bounds.data(); }
 };
 #endif

@@ -162,7 +162,7 @@ def test_render_matches_oracle(vx, gpu_worlds, mode):
     euler, cam_pos = (-0.45, 0.3, 0.0), (64, 90, 150)
     cam = vx.make_camera(cam_pos, euler, 90.0)
     ocam = ol.make_camera(cam_pos, euler, 90.0, tan_half=tan_half)
-    opts = vx.RenderOpts(mode["checkerboard"], mode["frame"], mode["debug_view"], mode["shadows"], 1, vx.NORM_HOST, 0, 0, 0, 0)
+    opts = vx.RenderOpts(mode["checkerboard"], mode["frame"], mode["debug_view"], mode["shadows"], 1, vx.NORM_HOST, 0, 0, 0, 0, None)
     oopts = ol.RenderOpts(mode["checkerboard"], mode["frame"], mode["debug_view"], mode["shadows"], 1, ol.NORM_HOST)
     rt = vx.VoxelRaytracer3D(w, 1)
     seed = np.full((H, W, 4), 7, np.uint8)  # unwritten pixels must keep this value

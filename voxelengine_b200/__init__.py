@@ -56,7 +56,8 @@ class Env(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("checkerboard", C.c_int32), ("frame_number", C.c_uint32), ("debug_view", C.c_int32),
                 ("shadows", C.c_int32), ("crosshair", C.c_int32), ("norm_mode", C.c_int32),
-                ("tile_x0", C.c_uint32), ("tile_y0", C.c_uint32), ("tile_w", C.c_uint32), ("tile_h", C.c_uint32)]
+                ("tile_x0", C.c_uint32), ("tile_y0", C.c_uint32), ("tile_w", C.c_uint32), ("tile_h", C.c_uint32),
+                ("d_stats", C.c_void_p)]
 
 
 # Every symbol include/vxrt.h declares (tests check that the library exports all of them).
@@ -64,7 +65,7 @@ ABI_SYMBOLS = [
     "vx_last_error", "vx_version", "vx_device_count", "vx_world_build_noise", "vx_world_build_noise_full",
     "vx_world_from_dense_bits", "vx_world_destroy", "vx_world_get_info", "vx_world_download", "vx_tracer_create",
     "vx_tracer_destroy", "vx_trace", "vx_trace_device", "vx_hits_postprocess", "vx_get_directions", "vx_render",
-    "vx_render_host", "vx_device_tanf", "vx_device_normalize",
+    "vx_render_host", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
 ]
 
 _lib = None
@@ -99,6 +100,7 @@ def lib():
     L.vx_render_host.argtypes = [vp, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts), vp, u32, u32]
     L.vx_device_tanf.argtypes = [C.c_float, C.POINTER(C.c_float), i32]
     L.vx_device_normalize.argtypes = [vp, vp, sz, i32]
+    L.vx_measure_read_bandwidth.argtypes = [i32, sz, i32, C.POINTER(C.c_float)]
     _lib = L
     return L
 
@@ -147,6 +149,13 @@ def default_env():
 def device_tanf(x, device=0):
     out = C.c_float(0)
     _check(lib().vx_device_tanf(float(x), C.byref(out), device))
+    return out.value
+
+
+def measure_read_bandwidth(nbytes, reps=20, device=0):
+    """GB/s of an all-SM streaming read of an nbytes buffer (L2-resident when nbytes << 126 MB)."""
+    out = C.c_float(0)
+    _check(lib().vx_measure_read_bandwidth(device, int(nbytes), int(reps), C.byref(out)))
     return out.value
 
 
@@ -278,5 +287,5 @@ def render_screen(rt, W, H, d_bgra, origin, fwd, up, right, env=None, fov_deg=90
     cam.up[:] = [float(v) for v in up]
     cam.right[:] = [float(v) for v in right]
     cam.fov_deg = fov_deg
-    opts = RenderOpts(int(checkerboard), frame_number, int(debug_view), int(shadows), 1, NORM_DEVICE, 0, 0, 0, 0)
+    opts = RenderOpts(int(checkerboard), frame_number, int(debug_view), int(shadows), 1, NORM_DEVICE, 0, 0, 0, 0, None)
     rt.render_device(cam, env or default_env(), opts, d_bgra, W, H, stream=stream)

@@ -53,17 +53,21 @@ __device__ __forceinline__ void put_pixel(uint8_t* __restrict__ bgra, uint32_t W
     reinterpret_cast<uint32_t*>(bgra)[(size_t)y * W + x] = b | (g << 8) | (r << 16) | 0xFF000000u;
 }
 
-template <int NORM>
-__device__ __forceinline__ V3 shade(const WorldView& w, const FrameParams& f, V3 n, V3 pos, int& extra_steps) {
+struct ShadowInfo { bool cast, hit; Work work; };
+
+template <int NORM, bool COUNT>
+__device__ __forceinline__ V3 shade(const WorldView& w, const FrameParams& f, V3 n, V3 pos, int& extra_steps, ShadowInfo& si) {
     // calculateColor, Renderer.cu:90-168 (AO block: samples = 0, no-op)
     extra_steps = 0;
     const V3 sray = normalize3<NORM>(f.light);
     const V3 spos = mk(fadd(pos.x, fmul(sray.x, 0.01f)), fadd(pos.y, fmul(sray.y, 0.01f)), fadd(pos.z, fmul(sray.z, 0.01f)));
     bool shadowed = false;
+    si.cast = false; si.hit = false; si.work.C = si.work.K = si.work.E = 0;
     if (f.shadows) {
         MarchOut m;
-        shadowed = march<NORM, false>(w, spos, sray, kMaxSteps, m);
+        shadowed = march<NORM, COUNT>(w, spos, sray, kMaxSteps, m);
         extra_steps += m.steps;
+        si.cast = true; si.hit = shadowed; si.work = m.work;
     }
     const float nl = dot3(n, f.light);
     const float ldot = fmul(fmaxf(nl, 0.0f), shadowed ? 0.0f : 1.0f);
@@ -84,20 +88,27 @@ __device__ __forceinline__ V3 shade(const WorldView& w, const FrameParams& f, V3
 
 // One thread per reference thread coordinate (tx,ty); a warp covers an 8x4 block of thread
 // coordinates instead of the reference's 32x1 strip (coherence), results are identical.
-template <int NORM>
-__global__ void __launch_bounds__(128) render_frame(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane) {
+//
+// STATS: accumulate per-frame ray/step/work counters into `stats` (8 x uint64: primary rays,
+// primary hits, shadow rays, shadow hits, steps, C, K, E — SURVEY.md §8d) with one atomic per warp.
+template <int NORM, bool STATS>
+__global__ void __launch_bounds__(128) render_frame(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
+                                                    unsigned long long* __restrict__ stats) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     // block = 4 warps = 16x8 thread coordinates; warp = 8x4
     const uint32_t tx = f.tx0 + blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
     const uint32_t ty = f.ty0 + blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
-    if (tx >= f.tx0 + f.tw || ty >= f.ty0 + f.th) return;
+    unsigned long long st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool live = !(tx >= f.tx0 + f.tw || ty >= f.ty0 + f.th);
     int x = (int)tx, y = (int)ty;
     if (f.checkerboard) { // Renderer.cu:186-194
         y *= 2;
         if ((x % 2) == 0) y += 1;
         if (f.frame_number % 2u == 0u) y += 1;
     }
-    if ((uint32_t)x >= f.W || (uint32_t)y >= f.H) return;
+    live = live && !((uint32_t)x >= f.W || (uint32_t)y >= f.H);
+    if (!STATS && !live) return;
+    if (live) {
     const int W = (int)f.W, H = (int)f.H;
     // getRayDirection, Renderer.cu:44-59
     const float u = fsub(fmul(fdiv((float)x, (float)W), 2.0f), 1.0f), v = fsub(fmul(fdiv((float)y, (float)H), 2.0f), 1.0f);
@@ -107,8 +118,9 @@ __global__ void __launch_bounds__(128) render_frame(WorldView w, FrameParams f, 
                fadd(fadd(f.fwd.z, fmul(a, f.right.z)), fmul(b, f.up.z)));
     rd = normalize3<NORM>(rd);
     MarchOut m;
-    const bool hit = march<NORM, false>(w, f.origin, rd, kMaxSteps, m);
+    const bool hit = march<NORM, STATS>(w, f.origin, rd, kMaxSteps, m);
     int steps = m.steps;
+    if (STATS) { st[0] = 1; st[1] = hit; st[5] = m.work.C; st[6] = m.work.K; st[7] = m.work.E; }
     const V3 n = mk(-m.normal.x, -m.normal.y, -m.normal.z);
     if (hit) {
         if (f.debug_view) { // Renderer.cu:215-243
@@ -122,7 +134,9 @@ __global__ void __launch_bounds__(128) render_frame(WorldView w, FrameParams f, 
             else put_pixel(bgra, f.W, f.H, x, y, mk(fmul(dist, 0.01f), 0.0f, 0.0f));
         } else {
             int extra = 0;
-            V3 c = shade<NORM>(w, f, n, m.pos, extra);
+            ShadowInfo si;
+            V3 c = shade<NORM, STATS>(w, f, n, m.pos, extra, si);
+            if (STATS) { st[2] = si.cast; st[3] = si.hit; st[5] += si.work.C; st[6] += si.work.K; st[7] += si.work.E; }
             c = mk(fdiv(c.x, fadd(c.x, 1.0f)), fdiv(c.y, fadd(c.y, 1.0f)), fdiv(c.z, fadd(c.z, 1.0f))); // Tonemap, Renderer.cu:170-177
             steps += extra;
             put_pixel(bgra, f.W, f.H, x, y, c);
@@ -133,6 +147,17 @@ __global__ void __launch_bounds__(128) render_frame(WorldView w, FrameParams f, 
     if (f.crosshair && tx == (f.W >> 1) && ty == (f.H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(10.0f, 10.0f, 10.0f));
     if (f.debug_view && x < (W >> 1) && y > (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(fdiv((float)steps, 256.0f), 0.0f, 0.0f));
     if (steps_plane) steps_plane[(size_t)y * f.W + x] = steps;
+    if (STATS) st[4] = (unsigned long long)steps;
+    } // live
+    if (STATS) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            unsigned long long v = st[k];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+            if (lane == 0 && v) atomicAdd(stats + k, v);
+        }
+    }
 }
 
 __global__ void tanf_kernel(float x, float* out) { *out = tanf(x); }
@@ -326,8 +351,15 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     if (f.tw == 0 || f.th == 0) return VX_OK;
     const dim3 grid((f.tw + 15u) / 16u, (f.th + 7u) / 8u);
     const WorldView w = t->world->view();
-    if (opts->norm_mode == VX_NORM_HOST) render_frame<1><<<grid, 128, 0, (cudaStream_t)stream>>>(w, f, (uint8_t*)d_bgra, d_steps);
-    else render_frame<0><<<grid, 128, 0, (cudaStream_t)stream>>>(w, f, (uint8_t*)d_bgra, d_steps);
+    unsigned long long* st = (unsigned long long*)opts->d_stats;
+    cudaStream_t cs = (cudaStream_t)stream;
+    if (opts->norm_mode == VX_NORM_HOST) {
+        if (st) render_frame<1, true><<<grid, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st);
+        else render_frame<1, false><<<grid, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, nullptr);
+    } else {
+        if (st) render_frame<0, true><<<grid, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st);
+        else render_frame<0, false><<<grid, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, nullptr);
+    }
     VX_CUDA(cudaGetLastError());
     return VX_OK;
 }
@@ -349,5 +381,50 @@ extern "C" int vx_render_host(vx_tracer* t, const vx_camera* cam, const vx_env* 
     if (rc) return rc;
     VX_CUDA(cudaMemcpyAsync(h_bgra, t->d_frame, bytes, cudaMemcpyDeviceToHost, t->stream));
     VX_CUDA(cudaStreamSynchronize(t->stream));
+    return VX_OK;
+}
+
+// ---- diagnostics: streaming-read bandwidth (L2-resident when `bytes` is well under the 126 MB L2) ----
+namespace vx {
+__global__ void __launch_bounds__(512) stream_read(const uint4* __restrict__ buf, size_t n16, int reps, unsigned* __restrict__ sink) {
+    unsigned acc = 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (int r = 0; r < reps; ++r)
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
+            uint4 v;
+            asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(buf + i));
+            acc ^= v.x ^ v.y ^ v.z ^ v.w;
+        }
+    if (acc == 0x9E3779B9u) *sink = acc; // never true for a zero buffer; keeps the loads alive
+}
+} // namespace vx
+
+extern "C" int vx_measure_read_bandwidth(int device, size_t bytes, int reps, float* gb_per_s) {
+    VX_REQUIRE(gb_per_s && bytes >= 4096 && reps > 0, "bad argument");
+    DeviceGuard guard(device);
+    if (!guard.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+    void* buf = nullptr; unsigned* sink = nullptr;
+    VX_CUDA(cudaMalloc(&buf, bytes));
+    VX_CUDA(cudaMalloc(&sink, 4));
+    VX_CUDA(cudaMemset(buf, 0, bytes));
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    cudaEvent_t e0, e1;
+    VX_CUDA(cudaEventCreate(&e0)); VX_CUDA(cudaEventCreate(&e1));
+    float best = 0.0f;
+    for (int trial = 0; trial < 5; ++trial) {
+        stream_read<<<sms * 4, 512>>>((const uint4*)buf, bytes / 16, trial == 0 ? 1 : reps, sink); // trial 0 warms the cache
+        if (trial == 0) continue;
+        VX_CUDA(cudaEventRecord(e0));
+        stream_read<<<sms * 4, 512>>>((const uint4*)buf, bytes / 16, reps, sink);
+        VX_CUDA(cudaEventRecord(e1));
+        VX_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.0f;
+        VX_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const float g = (float)((double)(bytes / 16 * 16) * reps / (ms * 1e-3) / 1e9);
+        if (g > best) best = g;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(buf); cudaFree(sink);
+    *gb_per_s = best;
     return VX_OK;
 }
