@@ -1,0 +1,370 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the brickmap ray tracer (contract: task brief, "Measurement").
+
+A step = one frame of the hot path: every pixel's primary ray through the two-level DDA plus, for
+every primary hit, the sun shadow ray and shading (BASELINE.json configs[2]/[3]).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload w2-4k|w2-8k|w1-1080p]
+
+N = 1   : 8192x512x8192 noise world, 8^3 bricks, 3840x2160, camera "overview" (SURVEY.md §8d config 3a).
+N > 1   : same world replicated on every GPU, 7680x4320 frame split into 8-row bands dealt round-robin
+          across ranks, framebuffer gathered to rank 0 with NCCL (config 4): strong scaling of one frame.
+--impl reference : the CPU restatement of the reference's path (oracle/, kind "port": the reference has no
+          CPU implementation of the 3-D march and its GPU build lives in oracle/_ref for parity only) on all
+          host cores, each step a bounded row sample of the same frame.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: dims, frame, camera (x,z), extra height, euler
+    "w2-4k": dict(dims=(8192, 512, 8192), W=3840, H=2160, xz=(4096, 7936), lift=128, euler=(-0.5, 0.0, 0.0),
+                  desc="8192x512x8192 noise brickmap (8^3 bricks), 3840x2160 primary + sun-shadow rays, overview camera"),
+    "w2-8k": dict(dims=(8192, 512, 8192), W=7680, H=4320, xz=(4096, 7936), lift=128, euler=(-0.5, 0.0, 0.0),
+                  desc="8192x512x8192 noise brickmap (8^3 bricks), 7680x4320 primary + sun-shadow rays, 8-row bands "
+                       "round-robin over ranks, NCCL gather to rank 0"),
+    "w1-1080p": dict(dims=(1024, 256, 1024), W=1920, H=1080, xz=(512, 960), lift=0, euler=(-0.45, 0.0, 0.0),
+                     desc="1024x256x1024 noise brickmap (8^3 bricks), 1920x1080 primary + sun-shadow rays"),
+}
+FACTOR = 8
+L2_FLUSH_BYTES = 512 << 20
+
+
+def read_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.path = tempfile.mktemp(prefix="clocks_", suffix=".csv")
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                c = [v.strip() for v in line.split(",")]
+                if len(c) < 7:
+                    continue
+                sm.append(float(c[0])); mx.append(float(c[1]))
+                for n, v in zip(names, c[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), samples=len(sm))
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def camera_for(vx, rt, wl):
+    """Camera height rule of SURVEY.md §8d: 16 above the highest solid voxel of the camera's column
+    (found with one vertical ray), Y+32 when the column is solid to the top; plus the workload's lift."""
+    X, Y, Z = wl["dims"]
+    x, z = wl["xz"]
+    r = rt.raytrace(np.array([[x + 0.5, Y + 10.0, z + 0.5]], np.float32), np.array([[0.0, -1.0, 0.0]], np.float32))
+    top = int(r["voxel"][0, 1]) if r["hit"][0] else -1
+    y = (top + 16 if top < Y - 1 else Y + 32) + wl["lift"]
+    return vx.make_camera((x, y, z), wl["euler"], 90.0), (float(x), float(y), float(z))
+
+
+def cpu_sample(ol, ow, wl, cam_pos, tan_half, target_s, threads):
+    """Times the CPU oracle on a bounded row sample of the workload frame; returns (Mrays/s, rays, seconds, stride)."""
+    W, H = wl["W"], wl["H"]
+    cam = ol.make_camera(cam_pos, wl["euler"], 90.0, tan_half=tan_half)
+    env = ol.default_env()
+    opts = ol.RenderOpts(0, 0, 0, 1, 1, ol.NORM_HOST)
+    # calibrate on 1/256 of the rows, then size the sample for about target_s seconds
+    stride = 256
+    t0 = time.perf_counter()
+    st = ow.render_sample(cam, env, opts, W, H, 0, H, stride, threads)
+    dt = time.perf_counter() - t0
+    rows_now = (H + stride - 1) // stride
+    rows_want = max(rows_now, min(H, int(rows_now * target_s / max(dt, 1e-3))))
+    stride = max(1, H // rows_want)
+    return cam, env, opts, stride
+
+
+def run_reference(args, wl, wl_name):
+    """--impl reference: the CPU port of the reference's march, all host threads, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    import voxelengine_b200 as vx
+    threads = os.cpu_count() or 1
+    X, Y, Z = wl["dims"]
+    # the world is the benchmark's INPUT: it is generated on the GPU (the CPU cannot generate 2^35 voxels of
+    # 32-octave noise in minutes) and handed to the CPU code in the reference's own form
+    world = vx.World.from_noise(X, Y, Z, FACTOR, device=0)
+    rt = vx.VoxelRaytracer3D(world, 16)
+    _, cam_pos = camera_for(vx, rt, wl)
+    fov = np.float32(np.float32(90.0 * 3.1415 / 180.0) / np.float32(2.0))
+    tan_half = vx.device_tanf(fov)
+    top, bw, b6 = world.download()
+    rt.close(); world.close()
+    ow = ol.OracleWorld.from_brickmap(top, bw, b6, X, Y, Z, FACTOR)
+    cam, env, opts, stride = cpu_sample(ol, ow, wl, cam_pos, tan_half, 2.0, threads)
+    W, H = wl["W"], wl["H"]
+    for _ in range(args.warmup):
+        ow.render_sample(cam, env, opts, W, H, 0, H, stride, threads)
+    rays = 0
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        st = ow.render_sample(cam, env, opts, W, H, k % stride, H, stride, threads)
+        rays += int(st[0] + st[2])
+    dt = time.perf_counter() - t0
+    val = rays / dt / 1e6
+    sample = "every %d-th pixel row of the %dx%d frame per step (%d rays/step), same world/camera as the GPU arm" % (
+        stride, W, H, rays // max(args.steps, 1))
+    line = {"impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt / max(args.steps, 1) * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl_name + ": " + wl["desc"], "camera": cam_pos, "timing": "host wall clock, CPU only"},
+            "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, wl, wl_name):
+    import torch
+    import torch.distributed as dist
+    import voxelengine_b200 as vx
+    import ctypes as C
+
+    rank = int(os.environ.get("RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world_size > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = local_rank
+    X, Y, Z = wl["dims"]
+    W, H = wl["W"], wl["H"]
+    world = vx.World.from_noise(X, Y, Z, FACTOR, device=dev)
+    info = world.info
+    rt = vx.VoxelRaytracer3D(world, 16)
+    cam, cam_pos = camera_for(vx, rt, wl)
+    env = vx.default_env()
+    stream = torch.cuda.current_stream().cuda_stream
+    nb = (H + 7) // 8                         # 8-row bands
+    per = (nb + world_size - 1) // world_size  # bands per rank, padded
+    frame = torch.zeros(nb * 8 * W * 4, dtype=torch.uint8, device="cuda")
+    frame_b = frame.view(nb, 8 * W * 4)
+    stats = torch.zeros(8, dtype=torch.int64, device="cuda")
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
+    send = torch.zeros(per, 8 * W * 4, dtype=torch.uint8, device="cuda") if world_size > 1 else None
+    recv = [torch.zeros_like(send) for _ in range(world_size)] if (world_size > 1 and rank == 0) else None
+    host = torch.empty(H * W * 4, dtype=torch.uint8).pin_memory() if rank == 0 else None
+
+    def opts(stats_ptr=None):
+        return vx.RenderOpts(0, 0, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, stats_ptr, world_size if world_size > 1 else 0, rank)
+
+    def render(o):
+        rt.render_device(cam, env, o, frame.data_ptr(), W, H, stream=stream)
+
+    def gather():
+        mine = frame_b[rank::world_size]
+        send[: mine.shape[0]].copy_(mine)
+        dist.gather(send, recv, dst=0)
+        if rank == 0:
+            for r in range(1, world_size):
+                dst = frame_b[r::world_size]
+                dst.copy_(recv[r][: dst.shape[0]])
+
+    # counters of exactly this frame (untimed counting variant of the kernel)
+    render(opts(stats.data_ptr()))
+    torch.cuda.synchronize()
+    st = stats.clone()
+    if world_size > 1:
+        dist.all_reduce(st)
+    st = st.cpu().numpy()
+    rays = int(st[0] + st[2])
+    alg_bytes_rank = int(4 * stats[5].item() + 8 * stats[6].item() + 64 * stats[7].item() + 4 * int(stats[0].item()))
+    o_timed = opts(None)
+    for _ in range(max(args.warmup, 3)):
+        flush.fill_(1)
+        render(o_timed)
+        if world_size > 1:
+            gather()
+    torch.cuda.synchronize()
+
+    # ---- timed region: K steps, device time by CUDA events on the launching stream -------------
+    sampler = ClockSampler(dev) if rank == 0 else None
+    if world_size > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    wall0 = time.perf_counter()
+    k_ms, step_ms = 0.0, 0.0
+    for _ in range(args.steps):
+        flush.fill_(1)  # L2 flush between timed iterations (512 MiB > 126 MB L2)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
+        render(o_timed)
+        e1.record()
+        if world_size > 1:
+            gather()
+        e2.record()
+        e2.synchronize()
+        k_ms += e0.elapsed_time(e1)
+        step_ms += e0.elapsed_time(e2)
+    torch.cuda.synchronize()
+    if world_size > 1:
+        dist.barrier()
+    wall = time.perf_counter() - wall0
+    t = torch.tensor([step_ms, k_ms], dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    step_ms_max, k_ms_max = (float(v) for v in t.cpu())
+    clocks = sampler.stop() if sampler else None
+
+    # ---- e2e: the reference-facing call with HOST buffers (RenderScreen + cudaMemcpy of main.cu:165-167) ----
+    e2e_rays_s = None
+    d2h = W * H * 4
+    h2d = C.sizeof(vx.Camera) + C.sizeof(vx.Env) + C.sizeof(vx.RenderOpts)
+    if world_size > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        if world_size == 1:
+            vx._check(vx.lib().vx_render_host(rt.h, C.byref(cam), C.byref(env), C.byref(o_timed), host.data_ptr(), W, H))
+        else:
+            render(o_timed)
+            gather()
+            if rank == 0:
+                host.copy_(frame[: H * W * 4], non_blocking=True)
+            torch.cuda.synchronize()
+    if world_size > 1:
+        dist.barrier()
+    e2e_s = time.perf_counter() - t0
+    e2e_rays_s = rays * args.steps / e2e_s / 1e6
+    return dict(vx=vx, rank=rank, world_size=world_size, rays=rays, st=st, alg_bytes_rank=alg_bytes_rank, step_ms=step_ms_max,
+                k_ms=k_ms_max, wall=wall, clocks=clocks, e2e=e2e_rays_s, h2d=h2d, d2h=d2h, info=info, cam_pos=cam_pos, world=world,
+                rt=rt, dev=dev)
+
+
+def cpu_baseline_leg(res, wl):
+    """N=1, rank 0: the oracle (CPU port of the reference's march) on a bounded sample of the same frame."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    vx = res["vx"]
+    threads = os.cpu_count() or 1
+    X, Y, Z = wl["dims"]
+    fov = np.float32(np.float32(90.0 * 3.1415 / 180.0) / np.float32(2.0))
+    tan_half = vx.device_tanf(fov, res["dev"])
+    top, bw, b6 = res["world"].download()
+    ow = ol.OracleWorld.from_brickmap(top, bw, b6, X, Y, Z, FACTOR)
+    cam, env, opts, stride = cpu_sample(ol, ow, wl, res["cam_pos"], tan_half, 12.0, threads)
+    t0 = time.perf_counter()
+    st = ow.render_sample(cam, env, opts, wl["W"], wl["H"], stride // 2, wl["H"], stride, threads)
+    dt = time.perf_counter() - t0
+    rays = int(st[0] + st[2])
+    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
+            "sample": "every %d-th pixel row of the %dx%d frame (%d rays, %.1f s), same world and camera" % (stride, wl["W"], wl["H"], rays, dt),
+            "steps_per_ray": float(st[4]) / max(rays, 1)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    wl_name = args.workload or ("w2-4k" if max(args.gpus, world_size) == 1 else "w2-8k")
+    wl = WORKLOADS[wl_name]
+    if args.impl == "reference":
+        run_reference(args, wl, wl_name)
+        return
+    res = run_ours(args, wl, wl_name)
+    if res["rank"] != 0:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+        return
+    vx = res["vx"]
+    K = args.steps
+    ms_step = res["step_ms"] / K
+    ms_kernel = res["k_ms"] / K
+    value = res["rays"] / (ms_step * 1e-3) / 1e6
+    hbm_peak, peak_src = read_peaks()
+    achieved = res["alg_bytes_rank"] / (ms_kernel * 1e-3) / 1e9
+    l2_peak = vx.measure_read_bandwidth(32 << 20, 50, res["dev"])
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(wl_name)
+    except Exception:
+        pass
+    st = res["st"]
+    line = {
+        "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": res["world_size"], "steps": K, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl_name + ": " + wl["desc"], "camera": res["cam_pos"], "euler": wl["euler"], "fov_deg": 90,
+                   "rays_per_step": res["rays"], "primary_rays": int(st[0]), "shadow_rays": int(st[2]), "steps_per_ray": float(st[4]) / res["rays"],
+                   "parallelism": "image bands x%d, world replicated" % res["world_size"], "l2": "flushed between timed steps (512 MiB write)",
+                   "world": {"occupied_bricks": int(res["info"].occupied_bricks), "bricks": int(res["info"].bricks),
+                             "pool_mb": res["info"].bytes_pool / 1e6, "build_ms": res["info"].build_ms}},
+        "clocks": res["clocks"],
+        "e2e": {"value": res["e2e"], "unit": "Mrays/s", "h2d_bytes_per_step": res["h2d"], "d2h_bytes_per_step": res["d2h"]},
+        "gpu_launches": K,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
+                     "peak_source": peak_src, "kernel": "vx::render_frame", "kernel_ms": ms_kernel,
+                     "algorithmic_bytes_per_launch": res["alg_bytes_rank"], "formula": "4*C + 8*K + 64*E + 4*pixels (SURVEY.md 8d)",
+                     "l2_peak_gbs_measured": l2_peak, "frac_of_l2": achieved / l2_peak},
+        "wall_s_timed_region": res["wall"],
+    }
+    if res["world_size"] == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_leg(res, wl)
+    print(json.dumps(line), flush=True)
+    if res["world_size"] > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

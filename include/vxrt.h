@@ -146,6 +146,9 @@ typedef struct vx_render_opts {
     uint64_t* d_stats;     /* optional DEVICE pointer to 8 counters the frame adds to: primary rays, primary
                               hits, shadow rays, shadow hits, steps, C, K, E (work counters of vx_hits);
                               the counting variant of the kernel is slower — leave NULL when timing */
+    uint32_t band_count, band_index; /* multi-GPU frame partition: the frame's 8-row bands are dealt round-robin
+                              to band_count devices; this call renders the bands == band_index (mod band_count)
+                              into their true positions of d_bgra.  band_count = 0: the whole frame */
 } vx_render_opts;
 
 void vx_get_directions(const float euler_xyz[3], float fwd[3], float up[3], float right[3]); /* Renderer.cu:27-42 */

@@ -105,6 +105,13 @@ void vxo_get_directions(const float euler[3], float fwd[3], float up[3], float r
 void vxo_render(const vxo_world* w, const vxo_camera* cam, const vxo_env* env, const vxo_render_opts* o,
                 uint32_t W, uint32_t H, uint8_t* bgra, int32_t* steps_plane, int nthreads);
 
+/* bounded sample of a frame (every ty_stride-th thread row in [ty_begin, ty_end)) for the timed CPU
+ * baseline; bgra may be NULL; stats_out[8] = primary rays, primary hits, shadow rays, shadow hits,
+ * steps, C, K, E */
+void vxo_render_sample(const vxo_world* w, const vxo_camera* cam, const vxo_env* env, const vxo_render_opts* o,
+                       uint32_t W, uint32_t H, uint32_t ty_begin, uint32_t ty_end, uint32_t ty_stride,
+                       uint8_t* bgra, uint64_t* stats_out, int nthreads);
+
 #ifdef __cplusplus
 }
 #endif

@@ -16,6 +16,8 @@
 #include "vxo_common.h"
 #include "vxo_trace.h"
 #include "vxo_world.h"
+#include <atomic>
+#include <mutex>
 
 using namespace vxo;
 
@@ -43,9 +45,12 @@ struct Frame {
     uint32_t W, H; uint8_t* bgra; int32_t* steps_plane;
     float tan_half;
 };
+/* per-thread accumulators of vxo_render_sample: primary rays, primary hits, shadow rays, shadow hits,
+ * steps, C, K, E (same order as vx_render_opts::d_stats) */
+struct Tally { uint64_t v[8] = {0, 0, 0, 0, 0, 0, 0, 0}; };
 
 void put(const Frame& f, int x, int y, V3 c) {
-    if ((uint32_t)x >= f.W || (uint32_t)y >= f.H) return;
+    if (!f.bgra || (uint32_t)x >= f.W || (uint32_t)y >= f.H) return;
     uint8_t* p = f.bgra + ((size_t)y * f.W + x) * 4;
     c.x = fmin_cu(fmax_cu(c.x, 0.0f), 1.0f);
     c.y = fmin_cu(fmax_cu(c.y, 0.0f), 1.0f);
@@ -71,7 +76,7 @@ V3 primary_dir(const Frame& f, int x, int y) {
     return norm3(d, f.o->norm_mode);
 }
 
-V3 shade(const Frame& f, V3 cam, V3 n, V3 pos, int& extra_steps) {
+V3 shade(const Frame& f, V3 cam, V3 n, V3 pos, int& extra_steps, Tally* tl) {
     const V3 L{f.env->light_dir[0], f.env->light_dir[1], f.env->light_dir[2]};
     const V3 LC{f.env->light_color[0], f.env->light_color[1], f.env->light_color[2]};
     const V3 AC{f.env->ambient[0], f.env->ambient[1], f.env->ambient[2]};
@@ -83,6 +88,7 @@ V3 shade(const Frame& f, V3 cam, V3 n, V3 pos, int& extra_steps) {
         MarchOut m;
         shadowed = march(*f.w, spos, sray, f.o->norm_mode, kMaxSteps, m);
         extra_steps += m.steps;
+        if (tl) { tl->v[2] += 1; tl->v[3] += shadowed; tl->v[5] += m.work.C; tl->v[6] += m.work.K; tl->v[7] += m.work.E; }
     }
     const float ldot = fmax_cu(dot3(n, L), 0.0f) * (shadowed ? 0.0f : 1.0f);
     const float up_dot = dot3(n, V3{0, 1, 0});
@@ -100,7 +106,7 @@ V3 shade(const Frame& f, V3 cam, V3 n, V3 pos, int& extra_steps) {
     return c;
 }
 
-void pixel(const Frame& f, int tx, int ty) {
+void pixel(const Frame& f, int tx, int ty, Tally* tl = nullptr) {
     int x = tx, y = ty;
     if (f.o->checkerboard) {
         y *= 2;
@@ -114,6 +120,7 @@ void pixel(const Frame& f, int tx, int ty) {
     MarchOut m;
     const bool hit = march(*f.w, origin, rd, f.o->norm_mode, kMaxSteps, m);
     int steps = m.steps;
+    if (tl) { tl->v[0] += 1; tl->v[1] += hit; tl->v[5] += m.work.C; tl->v[6] += m.work.K; tl->v[7] += m.work.E; }
     const V3 n{-m.normal.x, -m.normal.y, -m.normal.z};
     if (hit) {
         if (f.o->debug_view) {
@@ -127,7 +134,7 @@ void pixel(const Frame& f, int tx, int ty) {
             else put(f, x, y, V3{dist * 0.01f, 0, 0});
         } else {
             int extra = 0;
-            V3 c = shade(f, origin, n, m.pos, extra);
+            V3 c = shade(f, origin, n, m.pos, extra, tl);
             c = V3{c.x / (c.x + 1.0f), c.y / (c.y + 1.0f), c.z / (c.z + 1.0f)};
             c.x = fmin_cu(fmax_cu(c.x, 0.0f), 1.0f); c.y = fmin_cu(fmax_cu(c.y, 0.0f), 1.0f); c.z = fmin_cu(fmax_cu(c.z, 0.0f), 1.0f);
             steps += extra;
@@ -139,6 +146,7 @@ void pixel(const Frame& f, int tx, int ty) {
     if (f.o->crosshair && (uint32_t)tx == (f.W >> 1) && (uint32_t)ty == (f.H >> 1)) put(f, x, y, V3{10, 10, 10});
     if (f.o->debug_view && x < (W >> 1) && y > (H >> 1)) put(f, x, y, V3{(float)steps / 256.0f, 0, 0});
     if (f.steps_plane) f.steps_plane[(size_t)y * f.W + x] = steps;
+    if (tl) tl->v[4] += (uint64_t)steps;
 }
 
 } // namespace
@@ -157,4 +165,37 @@ extern "C" void vxo_render(const vxo_world* w, const vxo_camera* cam, const vxo_
         for (size_t ty = lo; ty < hi; ++ty)
             for (uint32_t tx = 0; tx < cols; ++tx) pixel(f, (int)tx, (int)ty);
     });
+}
+
+/* A bounded sample of a frame for the timed CPU baseline: thread rows ty_begin, ty_begin+ty_stride, ...
+ * < ty_end (clamped to the frame's grid).  bgra may be NULL (nothing is stored).  stats_out[8] receives
+ * primary rays, primary hits, shadow rays, shadow hits, steps, C, K, E of the sample. */
+extern "C" void vxo_render_sample(const vxo_world* w, const vxo_camera* cam, const vxo_env* env, const vxo_render_opts* o,
+                                  uint32_t W, uint32_t H, uint32_t ty_begin, uint32_t ty_end, uint32_t ty_stride,
+                                  uint8_t* bgra, uint64_t* stats_out, int nthreads) {
+    Frame f{w, cam, env, o, W, H, bgra, nullptr, 0.0f};
+    if (cam->tan_half > 0.0f) f.tan_half = cam->tan_half;
+    else {
+        const float fov = (float)((double)cam->fov_deg * 3.1415 / 180.0);
+        f.tan_half = std::tan(fov / 2.0f);
+    }
+    const uint32_t rows = o->checkerboard ? (H >> 1) : H;
+    if (ty_end > rows) ty_end = rows;
+    if (ty_stride == 0) ty_stride = 1;
+    const uint32_t cols = (W + 31) / 32 * 32;
+    const size_t nrows = ty_end > ty_begin ? (ty_end - ty_begin + ty_stride - 1) / ty_stride : 0;
+    if (nthreads <= 0) nthreads = (int)std::thread::hardware_concurrency();
+    if (nthreads < 1) nthreads = 1;
+    std::vector<Tally> tallies((size_t)nthreads * 16 + 1);
+    std::atomic<size_t> slot{0};
+    parallel_for(nrows, nthreads, [&](size_t lo, size_t hi) {
+        Tally local;
+        for (size_t r = lo; r < hi; ++r)
+            for (uint32_t tx = 0; tx < cols; ++tx) pixel(f, (int)tx, (int)(ty_begin + r * ty_stride), &local);
+        Tally& dst = tallies[slot.fetch_add(1) % tallies.size()];
+        static std::mutex mu;
+        std::lock_guard<std::mutex> g(mu);
+        for (int k = 0; k < 8; ++k) dst.v[k] += local.v[k];
+    });
+    for (int k = 0; k < 8; ++k) { stats_out[k] = 0; for (auto& t : tallies) stats_out[k] += t.v[k]; }
 }

@@ -83,6 +83,11 @@ def lib():
         L.vxo_render.restype = None
         L.vxo_render.argtypes = [C.c_void_p, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts),
                                  C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
+        L.vxo_render_sample.restype = None
+        L.vxo_render_sample.argtypes = [C.c_void_p, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts), C.c_uint32,
+                                        C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
+        L.vxo_world_from_brickmap_view.restype = C.c_void_p
+        L.vxo_world_from_brickmap_view.argtypes = [_u32p, _u32p, _f32p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int]
         _lib = L
     return _lib
 
@@ -113,6 +118,22 @@ class OracleWorld:
     def from_dense(cls, bits, X, Y, Z, factor=8):
         bits = np.ascontiguousarray(bits, np.uint32)
         return cls(lib().vxo_world_from_dense(bits, X, Y, Z, factor), X, Y, Z, factor)
+
+    @classmethod
+    def from_brickmap(cls, top, brick_bits, bounds, X, Y, Z, factor=8):
+        """Non-owning view of a reference-form brickmap (e.g. vx.World.download()); no dense grid."""
+        top = np.ascontiguousarray(top, np.uint32)
+        brick_bits = np.ascontiguousarray(brick_bits, np.uint32)
+        bounds = np.ascontiguousarray(bounds, np.float32).reshape(-1)
+        self = cls(lib().vxo_world_from_brickmap_view(top, brick_bits, bounds, X, Y, Z, factor), X, Y, Z, factor)
+        self._keep = (top, brick_bits, bounds)
+        return self
+
+    def render_sample(self, cam, env, opts, W, H, ty_begin, ty_end, ty_stride, nthreads=0):
+        stats = np.zeros(8, np.uint64)
+        lib().vxo_render_sample(self.h, C.byref(cam), C.byref(env), C.byref(opts), W, H, ty_begin, ty_end, ty_stride,
+                                None, stats.ctypes.data, nthreads)
+        return stats
 
     def __del__(self):
         if getattr(self, "h", None):

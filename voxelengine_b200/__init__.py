@@ -57,7 +57,7 @@ class RenderOpts(C.Structure):
     _fields_ = [("checkerboard", C.c_int32), ("frame_number", C.c_uint32), ("debug_view", C.c_int32),
                 ("shadows", C.c_int32), ("crosshair", C.c_int32), ("norm_mode", C.c_int32),
                 ("tile_x0", C.c_uint32), ("tile_y0", C.c_uint32), ("tile_w", C.c_uint32), ("tile_h", C.c_uint32),
-                ("d_stats", C.c_void_p)]
+                ("d_stats", C.c_void_p), ("band_count", C.c_uint32), ("band_index", C.c_uint32)]
 
 
 # Every symbol include/vxrt.h declares (tests check that the library exports all of them).

@@ -43,6 +43,7 @@ struct FrameParams {
     uint32_t frame_number;
     int checkerboard, debug_view, shadows, crosshair;
     uint32_t tx0, ty0, tw, th; // thread-space rectangle
+    uint32_t band_count, band_index; // multi-GPU: 8-row bands dealt round-robin, this launch renders bands == index (mod count)
 };
 
 __device__ __forceinline__ void put_pixel(uint8_t* __restrict__ bgra, uint32_t W, uint32_t H, int x, int y, V3 c) {
@@ -97,7 +98,7 @@ __global__ void __launch_bounds__(128) render_frame(WorldView w, FrameParams f, 
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     // block = 4 warps = 16x8 thread coordinates; warp = 8x4
     const uint32_t tx = f.tx0 + blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
-    const uint32_t ty = f.ty0 + blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+    const uint32_t ty = f.ty0 + (blockIdx.y * f.band_count + f.band_index) * 8u + (warp >> 1) * 4u + (lane >> 3);
     unsigned long long st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool live = !(tx >= f.tx0 + f.tw || ty >= f.ty0 + f.th);
     int x = (int)tx, y = (int)ty;
@@ -337,6 +338,9 @@ static int fill_frame(vx_tracer* t, const vx_camera* cam, const vx_env* env, con
         f.tw = o->tile_x0 < cols ? (o->tile_w < cols - o->tile_x0 ? o->tile_w : cols - o->tile_x0) : 0;
         f.th = o->tile_y0 < rows ? (o->tile_h < rows - o->tile_y0 ? o->tile_h : rows - o->tile_y0) : 0;
     } else { f.tx0 = 0; f.ty0 = 0; f.tw = cols; f.th = rows; }
+    f.band_count = o->band_count ? o->band_count : 1u;
+    f.band_index = o->band_count ? o->band_index : 0u;
+    VX_REQUIRE(f.band_index < f.band_count, "band_index must be below band_count");
     return VX_OK;
 }
 
@@ -349,7 +353,10 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     int rc = fill_frame(t, cam, env, opts, W, H, f);
     if (rc) return rc;
     if (f.tw == 0 || f.th == 0) return VX_OK;
-    const dim3 grid((f.tw + 15u) / 16u, (f.th + 7u) / 8u);
+    const uint32_t bands = (f.th + 7u) / 8u;
+    const uint32_t my_bands = bands > f.band_index ? (bands - f.band_index + f.band_count - 1u) / f.band_count : 0u;
+    if (my_bands == 0) return VX_OK;
+    const dim3 grid((f.tw + 15u) / 16u, my_bands);
     const WorldView w = t->world->view();
     unsigned long long* st = (unsigned long long*)opts->d_stats;
     cudaStream_t cs = (cudaStream_t)stream;
