@@ -175,3 +175,37 @@ def test_render_matches_oracle(vx, gpu_worlds, mode):
     assert diff.max() <= 1, "max channel difference %d" % diff.max()
     assert (diff > 0).mean() < 0.01
     rt.close()
+
+
+def test_full_scale_frame_matches_oracle(vx):
+    """BASELINE config 2 scale: 1024x256x1024 world built on the device, handed to the oracle in the
+    reference's form; whole shaded + shadowed frame: identical written pixels, RGB within 1/255, and the
+    per-pixel step plane (primary + shadow DDA steps) bit-exact."""
+    import torch
+    X, Y, Z = 1024, 256, 1024
+    w = vx.World.from_noise(X, Y, Z, 8)
+    top, bw, b6 = w.download()
+    ow = ol.OracleWorld.from_brickmap(top, bw, b6, X, Y, Z, 8)
+    W, H = 960, 540
+    tan_half = vx.device_tanf(np.float32(np.float32(90.0 * 3.1415 / 180.0) / np.float32(2.0)))
+    rt = vx.VoxelRaytracer3D(w, 1)
+    probe = vx.VoxelRaytracer3D(w, 4)
+    for (px, pz), eul in [((512, 960), (-0.45, 0.0, 0.0)), ((300, 300), (-0.1, 0.8, 0.0))]:
+        r = probe.raytrace(np.array([[px + 0.5, Y + 10.0, pz + 0.5]], np.float32), np.array([[0, -1, 0]], np.float32))
+        top_y = int(r["voxel"][0, 1]) if r["hit"][0] else -1
+        pos = (px, (top_y + 16 if top_y < Y - 1 else Y + 32), pz)  # camera height rule of SURVEY.md 8d
+        cam = vx.make_camera(pos, eul, 90.0)
+        ocam = ol.make_camera(pos, eul, 90.0, tan_half=tan_half)
+        frame = torch.full((H, W, 4), 7, dtype=torch.uint8, device="cuda")
+        steps = torch.full((H, W), -1, dtype=torch.int32, device="cuda")
+        opts = vx.RenderOpts(0, 0, 0, 1, 1, vx.NORM_HOST, 0, 0, 0, 0, None)
+        rt.render_device(cam, vx.default_env(), opts, frame.data_ptr(), W, H, d_steps=steps.data_ptr())
+        torch.cuda.synchronize()
+        got, gsteps = frame.cpu().numpy(), steps.cpu().numpy()
+        ref, rsteps = ow.render(ocam, ol.default_env(), ol.RenderOpts(0, 0, 0, 1, 1, ol.NORM_HOST), W, H,
+                                bgra=np.full((H, W, 4), 7, np.uint8))
+        assert np.array_equal(gsteps, rsteps), "step planes differ at %d pixels" % int((gsteps != rsteps).sum())
+        diff = np.abs(got.astype(np.int16) - ref.astype(np.int16))
+        assert diff.max() <= 1
+        assert gsteps.mean() > 5
+    probe.close(); rt.close(); w.close()

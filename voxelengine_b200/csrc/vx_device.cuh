@@ -53,154 +53,177 @@ __device__ __forceinline__ uint32_t tiled_index(int x, int y, int z, uint32_t ti
     return tile * 512u + (uint32_t)(x & 7) + ((uint32_t)(y & 7) << 3) + ((uint32_t)(z & 7) << 6);
 }
 
+// ---------------------------------------------------------------------------------------------
+// v2 DDA: branch-free step, per-ray invariants hoisted.  Same arithmetic, same
+// order of float operations per value as the reference; only control flow and evaluation
+// laziness differ (values the reference computes and never reads are not computed).
+// ---------------------------------------------------------------------------------------------
+struct Ray {
+    V3 d;
+    float ivx, ivy, ivz;   // slab test: 1/(d == 0 ? FLT_EPS : d)          VolumeRaytracer.cu:127-129
+    float dtx, dty, dtz;   // |1/d| or +inf                                :199-201
+    int sx, sy, sz;        // d > 0 ? 1 : -1                               :195-197
+};
+__device__ __forceinline__ Ray make_ray(V3 d) {
+    Ray r;
+    r.d = d;
+    r.ivx = fdiv(1.0f, d.x == 0.0f ? kFltEps : d.x);
+    r.ivy = fdiv(1.0f, d.y == 0.0f ? kFltEps : d.y);
+    r.ivz = fdiv(1.0f, d.z == 0.0f ? kFltEps : d.z);
+    // for d != 0 the slab inverse IS 1/d, so |1/d| reuses it bit for bit
+    r.dtx = d.x != 0.0f ? fabsf(r.ivx) : CUDART_INF_F;
+    r.dty = d.y != 0.0f ? fabsf(r.ivy) : CUDART_INF_F;
+    r.dtz = d.z != 0.0f ? fabsf(r.ivz) : CUDART_INF_F;
+    r.sx = d.x > 0.0f ? 1 : -1; r.sy = d.y > 0.0f ? 1 : -1; r.sz = d.z > 0.0f ? 1 : -1;
+    return r;
+}
+
 struct Slab { bool hit; V3 point; V3 normal; };
-__device__ __forceinline__ Slab ray_aabb(V3 s, V3 d, V3 lo, V3 hi) {
-    const float ivx = fdiv(1.0f, d.x == 0.0f ? kFltEps : d.x);
-    const float ivy = fdiv(1.0f, d.y == 0.0f ? kFltEps : d.y);
-    const float ivz = fdiv(1.0f, d.z == 0.0f ? kFltEps : d.z);
-    const float ax = fmul(fsub(lo.x, s.x), ivx), bx = fmul(fsub(hi.x, s.x), ivx);
-    const float ay = fmul(fsub(lo.y, s.y), ivy), by = fmul(fsub(hi.y, s.y), ivy);
-    const float az = fmul(fsub(lo.z, s.z), ivz), bz = fmul(fsub(hi.z, s.z), ivz);
+__device__ __forceinline__ Slab ray_aabb(V3 s, const Ray& r, V3 lo, V3 hi) {
+    const float ax = fmul(fsub(lo.x, s.x), r.ivx), bx = fmul(fsub(hi.x, s.x), r.ivx);
+    const float ay = fmul(fsub(lo.y, s.y), r.ivy), by = fmul(fsub(hi.y, s.y), r.ivy);
+    const float az = fmul(fsub(lo.z, s.z), r.ivz), bz = fmul(fsub(hi.z, s.z), r.ivz);
     const float nx = fminf(ax, bx), fx = fmaxf(ax, bx);
     const float ny = fminf(ay, by), fy = fmaxf(ay, by);
     const float nz = fminf(az, bz), fz = fmaxf(az, bz);
     const float t_in = fmaxf(fmaxf(nx, ny), nz);
     const float t_out = fminf(fminf(fx, fy), fz);
-    Slab r;
-    r.hit = !(t_out < fmaxf(t_in, 0.0f));
-    r.point = mk(fadd(s.x, fmul(t_in, d.x)), fadd(s.y, fmul(t_in, d.y)), fadd(s.z, fmul(t_in, d.z)));
-    if (t_in == nx) r.normal = mk(ivx < 0.0f ? -1.0f : 1.0f, 0.0f, 0.0f);
-    else if (t_in == ny) r.normal = mk(0.0f, ivy < 0.0f ? -1.0f : 1.0f, 0.0f);
-    else r.normal = mk(0.0f, 0.0f, ivz < 0.0f ? -1.0f : 1.0f);
-    return r;
+    Slab o;
+    o.hit = !(t_out < fmaxf(t_in, 0.0f));
+    o.point = mk(fadd(s.x, fmul(t_in, r.d.x)), fadd(s.y, fmul(t_in, r.d.y)), fadd(s.z, fmul(t_in, r.d.z)));
+    if (t_in == nx) o.normal = mk(r.ivx < 0.0f ? -1.0f : 1.0f, 0.0f, 0.0f);
+    else if (t_in == ny) o.normal = mk(0.0f, r.ivy < 0.0f ? -1.0f : 1.0f, 0.0f);
+    else o.normal = mk(0.0f, 0.0f, r.ivz < 0.0f ? -1.0f : 1.0f);
+    return o;
 }
 
-struct DdaOut {
-    bool hit, oob;
-    int cell[3];
-    int next[3];
-    V3 point, normal;
-    int steps;
+// Running state of one DDA level.
+struct Dda {
+    int cx, cy, cz;
+    float tx, ty, tz;
+    int limx, limy, limz; // exclusive upper cell limits incl. the reference's edge padding (:216-232)
 };
-
-// Per-ray constants of one DDA level.
-struct DdaSetup {
-    int cx, cy, cz, sx, sy, sz;
-    float tx, ty, tz, dtx, dty, dtz;
-    int limx, limy, limz; // exclusive upper cell limits incl. the reference's edge padding
-};
-__device__ __forceinline__ DdaSetup dda_setup(V3 s, V3 d, int cols, int rows, int depth) {
-    DdaSetup q;
+__device__ __forceinline__ Dda dda_begin(V3 s, const Ray& r, int cols, int rows, int depth) {
+    Dda q;
     q.cx = (int)s.x; q.cy = (int)s.y; q.cz = (int)s.z; // cvt.rzi: truncation, saturating
-    q.sx = d.x > 0.0f ? 1 : -1; q.sy = d.y > 0.0f ? 1 : -1; q.sz = d.z > 0.0f ? 1 : -1;
-    q.dtx = d.x != 0.0f ? fabsf(fdiv(1.0f, d.x)) : CUDART_INF_F;
-    q.dty = d.y != 0.0f ? fabsf(fdiv(1.0f, d.y)) : CUDART_INF_F;
-    q.dtz = d.z != 0.0f ? fabsf(fdiv(1.0f, d.z)) : CUDART_INF_F;
-    q.tx = d.x != 0.0f ? fdiv(fsub((float)(q.cx + (q.sx > 0)), s.x), d.x) : CUDART_INF_F;
-    q.ty = d.y != 0.0f ? fdiv(fsub((float)(q.cy + (q.sy > 0)), s.y), d.y) : CUDART_INF_F;
-    q.tz = d.z != 0.0f ? fdiv(fsub((float)(q.cz + (q.sz > 0)), s.z), d.z) : CUDART_INF_F;
-    const bool on_edge = q.cx == cols || q.cy == rows || q.cz == depth; // VolumeRaytracer.cu:216-232
-    q.limx = cols + ((on_edge && d.x < 0.0f) ? 1 : 0);
-    q.limy = rows + ((on_edge && d.y < 0.0f) ? 1 : 0);
-    q.limz = depth + ((on_edge && d.z < 0.0f) ? 1 : 0);
+    q.tx = r.d.x != 0.0f ? fdiv(fsub((float)(q.cx + (r.sx > 0)), s.x), r.d.x) : CUDART_INF_F;
+    q.ty = r.d.y != 0.0f ? fdiv(fsub((float)(q.cy + (r.sy > 0)), s.y), r.d.y) : CUDART_INF_F;
+    q.tz = r.d.z != 0.0f ? fdiv(fsub((float)(q.cz + (r.sz > 0)), s.z), r.d.z) : CUDART_INF_F;
+    const bool on_edge = q.cx == cols || q.cy == rows || q.cz == depth;
+    q.limx = cols + ((on_edge && r.d.x < 0.0f) ? 1 : 0);
+    q.limy = rows + ((on_edge && r.d.y < 0.0f) ? 1 : 0);
+    q.limz = depth + ((on_edge && r.d.z < 0.0f) ? 1 : 0);
     return q;
 }
-
-// Advance one cell along the smallest tMax (ties: y over x, z over both — VolumeRaytracer.cu:293-322).
-// Returns the axis advanced (0,1,2) and the face-crossing point.
-__device__ __forceinline__ int dda_advance(DdaSetup& q, V3 s, V3 d, V3& p) {
-    if (q.tx < q.ty && q.tx < q.tz) {
-        p = mk((float)(q.cx + (q.sx > 0)), fadd(s.y, fmul(q.tx, d.y)), fadd(s.z, fmul(q.tx, d.z)));
-        q.cx += q.sx; q.tx = fadd(q.tx, q.dtx);
-        return 0;
-    } else if (q.ty <= q.tx && q.ty < q.tz) {
-        p = mk(fadd(s.x, fmul(q.ty, d.x)), (float)(q.cy + (q.sy > 0)), fadd(s.z, fmul(q.ty, d.z)));
-        q.cy += q.sy; q.ty = fadd(q.ty, q.dty);
-        return 1;
-    } else {
-        p = mk(fadd(s.x, fmul(q.tz, d.x)), fadd(s.y, fmul(q.tz, d.y)), (float)(q.cz + (q.sz > 0)));
-        q.cz += q.sz; q.tz = fadd(q.tz, q.dtz);
-        return 2;
-    }
+__device__ __forceinline__ bool dda_inside(const Dda& q) {
+    return (unsigned)q.cx < (unsigned)q.limx && (unsigned)q.cy < (unsigned)q.limy && (unsigned)q.cz < (unsigned)q.limz;
 }
-__device__ __forceinline__ V3 axis_normal(int axis, const DdaSetup& q) {
-    return axis == 0 ? mk((float)q.sx, 0.0f, 0.0f) : (axis == 1 ? mk(0.0f, (float)q.sy, 0.0f) : mk(0.0f, 0.0f, (float)q.sz));
+// One cell along the smallest tMax (ties: y over x, z over both — :293-322), without branches.
+// Returns the axis masks and the parameter t of the crossing.
+__device__ __forceinline__ void dda_step(Dda& q, const Ray& r, bool& mx, bool& my, float& t) {
+    mx = q.tx < q.ty && q.tx < q.tz;
+    my = !mx && q.ty <= q.tx && q.ty < q.tz;
+    const bool mz = !mx && !my;
+    t = mx ? q.tx : (my ? q.ty : q.tz);
+    const float tn = fadd(t, mx ? r.dtx : (my ? r.dty : r.dtz));
+    q.tx = mx ? tn : q.tx; q.ty = my ? tn : q.ty; q.tz = mz ? tn : q.tz;
+    q.cx += mx ? r.sx : 0; q.cy += my ? r.sy : 0; q.cz += mz ? r.sz : 0;
 }
 
-// Coarse level: cells are bricks; a cell is a candidate when its occupancy bit is set and the ray
-// hits the brick's tight AABB (VolumeRaytracer.cu:248-273).  `rec_out` returns the record of the hit cell.
+struct CoarseOut {
+    bool hit, oob;
+    int steps;
+    int cell[3];
+    V3 point, normal;
+    uint2 rec;
+    Dda at_exit; // state before the reference's final advance; NextCell = one more dda_step (rarely needed)
+};
+
+// Coarse level: cells are bricks; a cell is a candidate when its occupancy bit is set and the ray hits
+// the brick's tight AABB (VolumeRaytracer.cu:248-273).  The crossing point / normal of plain steps are
+// never read by Raytrace for the coarse level (only a hit's AABB point/normal are), so they are not formed.
 template <bool COUNT>
-__device__ __forceinline__ void dda_coarse(const WorldView& w, V3 s, V3 d, DdaOut& r, uint2& rec_out, Work& wk) {
-    DdaSetup q = dda_setup(s, d, w.cx, w.cy, w.cz);
-    r.point = s; r.hit = false; r.oob = false; r.steps = 0;
-    r.cell[0] = r.cell[1] = r.cell[2] = 0;
-    r.normal = mk(0.0f, 0.0f, 0.0f);
+__device__ __forceinline__ void dda_coarse(const WorldView& w, V3 s, const Ray& r, CoarseOut& o, Work& wk) {
+    Dda q = dda_begin(s, r, w.cx, w.cy, w.cz);
+    o.hit = false; o.oob = false; o.steps = 0;
+    o.point = s; o.normal = mk(0.0f, 0.0f, 0.0f);
+    o.cell[0] = o.cell[1] = o.cell[2] = 0;
+    o.rec = make_uint2(0u, 0u);
+    const float inv_f = fdiv(1.0f, (float)w.factor); // exact for power-of-two factors
+    const bool pow2 = (w.factor & (w.factor - 1)) == 0;
     const float fs = (float)w.factor;
-    bool leave = false;
+    int steps = 0;
     for (int it = 0; it < kMaxSteps; ++it) {
-        if (0 <= q.cx && q.cx < q.limx && 0 <= q.cy && q.cy < q.limy && 0 <= q.cz && q.cz < q.limz) {
-            const int qx = min(q.cx, w.cx - 1), qy = min(q.cy, w.cy - 1), qz = min(q.cz, w.cz - 1);
-            r.cell[0] = qx; r.cell[1] = qy; r.cell[2] = qz;
-            const uint32_t idx = tiled_index(qx, qy, qz, w.tiles_x, w.tiles_xy);
-            const bool occ = (__ldg(w.top + (idx >> 5)) >> (idx & 31u)) & 1u;
-            if (COUNT) { wk.C++; wk.K += occ; }
-            if (occ) {
-                const uint2 rec = __ldg(w.records + idx);
-                const uint32_t b = rec.x;
-                const V3 lo = mk(fadd(fdiv((float)(b & 31u), fs), (float)qx), fadd(fdiv((float)((b >> 5) & 31u), fs), (float)qy),
-                                 fadd(fdiv((float)((b >> 10) & 31u), fs), (float)qz));
-                const V3 hi = mk(fadd(fdiv((float)(((b >> 15) & 31u) + 1u), fs), (float)qx),
-                                 fadd(fdiv((float)(((b >> 20) & 31u) + 1u), fs), (float)qy),
-                                 fadd(fdiv((float)(((b >> 25) & 31u) + 1u), fs), (float)qz));
-                const Slab sl = ray_aabb(s, d, lo, hi);
-                if (sl.hit) {
-                    r.hit = true; r.normal = sl.normal;
-                    if (it != 0) r.point = sl.point;
-                    rec_out = rec;
-                    leave = true;
-                }
+        if (!dda_inside(q)) { o.oob = true; break; }
+        const int qx = min(q.cx, w.cx - 1), qy = min(q.cy, w.cy - 1), qz = min(q.cz, w.cz - 1);
+        const uint32_t idx = tiled_index(qx, qy, qz, w.tiles_x, w.tiles_xy);
+        const bool occ = (__ldg(w.top + (idx >> 5)) >> (idx & 31u)) & 1u;
+        if (COUNT) { wk.C++; wk.K += occ; }
+        if (occ) {
+            const uint2 rec = __ldg(w.records + idx);
+            const uint32_t b = rec.x;
+            const float l0 = (float)(b & 31u), l1 = (float)((b >> 5) & 31u), l2 = (float)((b >> 10) & 31u);
+            const float h0 = (float)(((b >> 15) & 31u) + 1u), h1 = (float)(((b >> 20) & 31u) + 1u), h2 = (float)(((b >> 25) & 31u) + 1u);
+            // (min + 0) / scale + cell, (max + 1) / scale + cell — :250-255; x/2^k == x*2^-k exactly
+            const V3 lo = pow2 ? mk(fadd(fmul(l0, inv_f), (float)qx), fadd(fmul(l1, inv_f), (float)qy), fadd(fmul(l2, inv_f), (float)qz))
+                               : mk(fadd(fdiv(l0, fs), (float)qx), fadd(fdiv(l1, fs), (float)qy), fadd(fdiv(l2, fs), (float)qz));
+            const V3 hi = pow2 ? mk(fadd(fmul(h0, inv_f), (float)qx), fadd(fmul(h1, inv_f), (float)qy), fadd(fmul(h2, inv_f), (float)qz))
+                               : mk(fadd(fdiv(h0, fs), (float)qx), fadd(fdiv(h1, fs), (float)qy), fadd(fdiv(h2, fs), (float)qz));
+            const Slab sl = ray_aabb(s, r, lo, hi);
+            if (sl.hit) {
+                o.hit = true; o.normal = sl.normal;
+                if (it != 0) o.point = sl.point;
+                o.cell[0] = qx; o.cell[1] = qy; o.cell[2] = qz;
+                o.rec = rec;
+                break;
             }
-        } else {
-            r.oob = true; leave = true;
         }
-        V3 p;
-        const int axis = dda_advance(q, s, d, p);
-        if (leave) break;
-        r.normal = axis_normal(axis, q);
-        r.steps += 1;
-        r.point = p;
+        bool mx, my; float t;
+        dda_step(q, r, mx, my, t);
+        ++steps;
     }
-    r.next[0] = q.cx; r.next[1] = q.cy; r.next[2] = q.cz;
+    o.steps = steps;
+    o.at_exit = q;
 }
 
-// Fine level: cells are voxels of one brick (factor^3 bits, in-brick tiled index); crossing points
-// are tested against [0,factor]^3 before a step is counted (VolumeRaytracer.cu:325-341).
-__device__ __forceinline__ void dda_fine(const uint32_t* __restrict__ mask, int f, V3 s, V3 d, DdaOut& r) {
-    DdaSetup q = dda_setup(s, d, f, f, f);
-    r.point = s; r.hit = false; r.oob = false; r.steps = 0;
-    r.cell[0] = r.cell[1] = r.cell[2] = 0;
-    r.normal = mk(0.0f, 0.0f, 0.0f);
+struct FineOut {
+    bool hit, oob;
+    int steps;
+    int cell[3];
+    V3 point, normal;
+};
+
+// Fine level: cells are voxels of one brick; crossing points are tested against [0,factor]^3 before a step
+// is counted (VolumeRaytracer.cu:325-341).  FINE8: factor == 8, mask bit = x + 8y + 64z.
+template <bool FINE8>
+__device__ __forceinline__ void dda_fine(const uint32_t* __restrict__ mask, int f, V3 s, const Ray& r, FineOut& o) {
+    Dda q = dda_begin(s, r, f, f, f);
+    o.hit = false; o.oob = false;
+    o.point = s; o.normal = mk(0.0f, 0.0f, 0.0f);
+    o.cell[0] = o.cell[1] = o.cell[2] = 0;
     const uint32_t tiles = (uint32_t)f >> 3;
     const float hi = (float)f;
-    bool leave = false;
+    const int ox = r.sx > 0, oy = r.sy > 0, oz = r.sz > 0;
+    int steps = 0;
     for (int it = 0; it < kMaxSteps; ++it) {
-        if (0 <= q.cx && q.cx < q.limx && 0 <= q.cy && q.cy < q.limy && 0 <= q.cz && q.cz < q.limz) {
-            const int qx = min(q.cx, f - 1), qy = min(q.cy, f - 1), qz = min(q.cz, f - 1);
-            r.cell[0] = qx; r.cell[1] = qy; r.cell[2] = qz;
-            const uint32_t idx = tiled_index(qx, qy, qz, tiles, tiles * tiles);
-            if ((__ldg(mask + (idx >> 5)) >> (idx & 31u)) & 1u) { r.hit = true; leave = true; }
-        } else {
-            r.oob = true; leave = true;
+        if (!dda_inside(q)) { o.oob = true; break; }
+        const int qx = min(q.cx, f - 1), qy = min(q.cy, f - 1), qz = min(q.cz, f - 1);
+        const uint32_t idx = FINE8 ? (uint32_t)(qx + (qy << 3) + (qz << 6)) : tiled_index(qx, qy, qz, tiles, tiles * tiles);
+        if ((__ldg(mask + (idx >> 5)) >> (idx & 31u)) & 1u) {
+            o.hit = true; o.cell[0] = qx; o.cell[1] = qy; o.cell[2] = qz;
+            break;
         }
-        V3 p;
-        const int axis = dda_advance(q, s, d, p);
-        if (leave) break;
-        r.normal = axis_normal(axis, q);
-        if (p.x < 0.0f || p.x > hi || p.y < 0.0f || p.y > hi || p.z < 0.0f || p.z > hi) { r.oob = true; break; }
-        r.steps += 1;
-        r.point = p;
+        const float fx = (float)(q.cx + ox), fy = (float)(q.cy + oy), fz = (float)(q.cz + oz); // faces of the cell being left
+        bool mx, my; float t;
+        dda_step(q, r, mx, my, t);
+        const bool mz = !mx && !my;
+        const V3 p = mk(mx ? fx : fadd(s.x, fmul(t, r.d.x)), my ? fy : fadd(s.y, fmul(t, r.d.y)), mz ? fz : fadd(s.z, fmul(t, r.d.z)));
+        if (p.x < 0.0f || p.x > hi || p.y < 0.0f || p.y > hi || p.z < 0.0f || p.z > hi) { o.oob = true; break; }
+        ++steps;
+        o.point = p;
+        o.normal = mk(mx ? (float)r.sx : 0.0f, my ? (float)r.sy : 0.0f, mz ? (float)r.sz : 0.0f);
     }
-    r.next[0] = q.cx; r.next[1] = q.cy; r.next[2] = q.cz;
+    o.steps = steps;
 }
 
 struct MarchOut {
@@ -222,32 +245,31 @@ __device__ __forceinline__ bool march(const WorldView& w, V3 origin, V3 ray, int
     o.voxel[0] = o.voxel[1] = o.voxel[2] = -1;
     o.work.C = o.work.K = o.work.E = 0;
     V3 start = mk(fdiv(origin.x, ff), fdiv(origin.y, ff), fdiv(origin.z, ff));
-    const V3 d = normalize3<NORM>(ray);
+    const Ray r = make_ray(normalize3<NORM>(ray));
     V3 start_normal = mk(0.0f, 0.0f, 0.0f);
     if (!(start.x >= 0.0f && start.y >= 0.0f && start.z >= 0.0f && start.x < (float)w.cx && start.y < (float)w.cy &&
           start.z < (float)w.cz)) {
         const float e = (float)kEpsDDA;
-        const Slab sl = ray_aabb(start, d, mk(e, e, e),
+        const Slab sl = ray_aabb(start, r, mk(e, e, e),
                                  mk((float)((double)w.cx - kEpsDDA), (float)((double)w.cy - kEpsDDA), (float)((double)w.cz - kEpsDDA)));
         if (sl.hit) { start = sl.point; start_normal = sl.normal; }
     }
     V3 normal = mk(0.0f, 0.0f, 0.0f), hit_pos = mk(0.0f, 0.0f, 0.0f);
     bool hit = false;
     while (total < max_steps) {
-        DdaOut c;
-        uint2 rec = make_uint2(0u, 0u);
-        dda_coarse<COUNT>(w, start, d, c, rec, o.work);
+        CoarseOut c;
+        dda_coarse<COUNT>(w, start, r, c, o.work);
         total += c.steps; o.coarse_steps += c.steps;
-        V3 local = mk(fmul(c.point.x, ff), fmul(c.point.y, ff), fmul(c.point.z, ff));
-        hit_pos = local;
-        if (!(c.hit && !c.oob)) break;
-        if (pcx == c.cell[0] && pcy == c.cell[1] && pcz == c.cell[2]) break; // VolumeRaytracer.cu:402-407
+        if (!c.hit) break; // miss or out of bounds (:508-511); hitPosition is not read on a miss
+        if (pcx == c.cell[0] && pcy == c.cell[1] && pcz == c.cell[2]) break; // :402-407
         pcx = c.cell[0]; pcy = c.cell[1]; pcz = c.cell[2];
         const float bx = fmul((float)pcx, ff), by = fmul((float)pcy, ff), bz = fmul((float)pcz, ff);
-        local = mk(fsub(local.x, bx), fsub(local.y, by), fsub(local.z, bz));
+        const V3 local = mk(fsub(fmul(c.point.x, ff), bx), fsub(fmul(c.point.y, ff), by), fsub(fmul(c.point.z, ff), bz));
         if (COUNT) o.work.E++;
-        DdaOut q;
-        dda_fine(w.pool + (size_t)rec.y * w.words_per_brick, w.factor, local, d, q);
+        FineOut q;
+        const uint32_t* mask = w.pool + (size_t)c.rec.y * w.words_per_brick;
+        if (w.factor == 8) dda_fine<true>(mask, 8, local, r, q);
+        else dda_fine<false>(mask, w.factor, local, r, q);
         total += q.steps; o.fine_steps += q.steps;
         hit_pos = mk(fadd(q.point.x, bx), fadd(q.point.y, by), fadd(q.point.z, bz));
         if (q.hit) {
@@ -258,14 +280,16 @@ __device__ __forceinline__ bool march(const WorldView& w, V3 origin, V3 ray, int
             break;
         }
         start = mk(fdiv(hit_pos.x, ff), fdiv(hit_pos.y, ff), fdiv(hit_pos.z, ff));
-        if (q.oob) { // VolumeRaytracer.cu:438-489
-            const bool ex = pcx == (int)start.x, ey = pcy == (int)start.y, ez = pcz == (int)start.z;
-            if (ex && ey && ez) {
-                start.x = nextafterf(start.x, d.x < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
-                start.y = nextafterf(start.y, d.y < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
-                start.z = nextafterf(start.z, d.z < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
+        if (q.oob) { // :438-489
+            if (pcx == (int)start.x && pcy == (int)start.y && pcz == (int)start.z) {
+                start.x = nextafterf(start.x, r.d.x < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
+                start.y = nextafterf(start.y, r.d.y < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
+                start.z = nextafterf(start.z, r.d.z < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
                 if (pcx == (int)start.x && pcy == (int)start.y && pcz == (int)start.z) {
-                    const float gx = fsub((float)c.next[0], start.x), gy = fsub((float)c.next[1], start.y), gz = fsub((float)c.next[2], start.z);
+                    Dda n = c.at_exit; // NextCell of the COARSE traversal = the cell after its final advance (:347,:473)
+                    bool mx, my; float t;
+                    dda_step(n, r, mx, my, t);
+                    const float gx = fsub((float)n.cx, start.x), gy = fsub((float)n.cy, start.y), gz = fsub((float)n.cz, start.z);
                     const float ax = fabsf(gx), ay = fabsf(gy), az = fabsf(gz);
                     if (ax < ay && ax < az) start.x = fadd(start.x, gx);
                     else if (ay < ax && ay < az) start.y = fadd(start.y, gy);
