@@ -25,6 +25,11 @@ struct WorldView {
     int factor;
     uint32_t words_per_brick;           // factor^3 / 32
     uint32_t tiles_x, tiles_xy;         // cx/8, (cx/8)*(cy/8)
+    // traversal copies in our own layout: x-fastest linear grid with a one-cell border on every side
+    // (dims cx+2, cy+2, cz+2); border bits are 1 so that leaving the grid shows up as an "occupied" lookup
+    const uint32_t* __restrict__ ptop;  // padded occupancy bits
+    const uint2* __restrict__ precords; // padded records (same packing as `records`)
+    int pnx, pnxy;                      // cx+2, (cx+2)*(cy+2)
 };
 
 struct Work { uint32_t C, K, E; };
@@ -139,9 +144,39 @@ struct CoarseOut {
     Dda at_exit; // state before the reference's final advance; NextCell = one more dda_step (rarely needed)
 };
 
-// Coarse level: cells are bricks; a cell is a candidate when its occupancy bit is set and the ray hits
-// the brick's tight AABB (VolumeRaytracer.cu:248-273).  The crossing point / normal of plain steps are
-// never read by Raytrace for the coarse level (only a hit's AABB point/normal are), so they are not formed.
+// Occupied coarse cell (qx,qy,qz): build the brick's tight AABB from its packed bounds and slab-test it
+// ((min + 0) / scale + cell, (max + 1) / scale + cell — VolumeRaytracer.cu:248-273).
+__device__ __forceinline__ bool coarse_candidate(const WorldView& w, V3 s, const Ray& r, int qx, int qy, int qz, uint2 rec, int it, CoarseOut& o) {
+    const uint32_t b = rec.x;
+    const float l0 = (float)(b & 31u), l1 = (float)((b >> 5) & 31u), l2 = (float)((b >> 10) & 31u);
+    const float h0 = (float)(((b >> 15) & 31u) + 1u), h1 = (float)(((b >> 20) & 31u) + 1u), h2 = (float)(((b >> 25) & 31u) + 1u);
+    V3 lo, hi;
+    if ((w.factor & (w.factor - 1)) == 0) { // x / 2^k == x * 2^-k exactly
+        const float inv_f = fdiv(1.0f, (float)w.factor);
+        lo = mk(fadd(fmul(l0, inv_f), (float)qx), fadd(fmul(l1, inv_f), (float)qy), fadd(fmul(l2, inv_f), (float)qz));
+        hi = mk(fadd(fmul(h0, inv_f), (float)qx), fadd(fmul(h1, inv_f), (float)qy), fadd(fmul(h2, inv_f), (float)qz));
+    } else {
+        const float fs = (float)w.factor;
+        lo = mk(fadd(fdiv(l0, fs), (float)qx), fadd(fdiv(l1, fs), (float)qy), fadd(fdiv(l2, fs), (float)qz));
+        hi = mk(fadd(fdiv(h0, fs), (float)qx), fadd(fdiv(h1, fs), (float)qy), fadd(fdiv(h2, fs), (float)qz));
+    }
+    const Slab sl = ray_aabb(s, r, lo, hi);
+    if (!sl.hit) return false;
+    o.hit = true; o.normal = sl.normal;
+    if (it != 0) o.point = sl.point;
+    o.cell[0] = qx; o.cell[1] = qy; o.cell[2] = qz;
+    o.rec = rec;
+    return true;
+}
+
+// Coarse level: cells are bricks.  The crossing point / normal of plain steps are never read by Raytrace
+// for the coarse level (only a hit's AABB point/normal are), so they are not formed.
+//
+// Two loops with identical step semantics:
+//  * a generic one (explicit bounds test, clamped lookups) that runs while the current cell is not strictly
+//    inside the grid — i.e. the ray starts outside, or sits on the reference's padded far face (:216-232);
+//  * the hot one over the bordered linear grid: the cell index advances by a per-axis constant, leaving the
+//    grid is detected by the border's sentinel bits, and cell coordinates are only recovered at events.
 template <bool COUNT>
 __device__ __forceinline__ void dda_coarse(const WorldView& w, V3 s, const Ray& r, CoarseOut& o, Work& wk) {
     Dda q = dda_begin(s, r, w.cx, w.cy, w.cz);
@@ -149,41 +184,44 @@ __device__ __forceinline__ void dda_coarse(const WorldView& w, V3 s, const Ray& 
     o.point = s; o.normal = mk(0.0f, 0.0f, 0.0f);
     o.cell[0] = o.cell[1] = o.cell[2] = 0;
     o.rec = make_uint2(0u, 0u);
-    const float inv_f = fdiv(1.0f, (float)w.factor); // exact for power-of-two factors
-    const bool pow2 = (w.factor & (w.factor - 1)) == 0;
-    const float fs = (float)w.factor;
-    int steps = 0;
-    for (int it = 0; it < kMaxSteps; ++it) {
-        if (!dda_inside(q)) { o.oob = true; break; }
+    int it = 0;
+    bool done = false;
+    while (it < kMaxSteps && !((unsigned)q.cx < (unsigned)w.cx && (unsigned)q.cy < (unsigned)w.cy && (unsigned)q.cz < (unsigned)w.cz)) {
+        if (!dda_inside(q)) { o.oob = true; done = true; break; }
         const int qx = min(q.cx, w.cx - 1), qy = min(q.cy, w.cy - 1), qz = min(q.cz, w.cz - 1);
-        const uint32_t idx = tiled_index(qx, qy, qz, w.tiles_x, w.tiles_xy);
-        const bool occ = (__ldg(w.top + (idx >> 5)) >> (idx & 31u)) & 1u;
+        const uint32_t idx = (uint32_t)((qz + 1) * w.pnxy + (qy + 1) * w.pnx + (qx + 1));
+        const bool occ = (__ldg(w.ptop + (idx >> 5)) >> (idx & 31u)) & 1u;
         if (COUNT) { wk.C++; wk.K += occ; }
-        if (occ) {
-            const uint2 rec = __ldg(w.records + idx);
-            const uint32_t b = rec.x;
-            const float l0 = (float)(b & 31u), l1 = (float)((b >> 5) & 31u), l2 = (float)((b >> 10) & 31u);
-            const float h0 = (float)(((b >> 15) & 31u) + 1u), h1 = (float)(((b >> 20) & 31u) + 1u), h2 = (float)(((b >> 25) & 31u) + 1u);
-            // (min + 0) / scale + cell, (max + 1) / scale + cell — :250-255; x/2^k == x*2^-k exactly
-            const V3 lo = pow2 ? mk(fadd(fmul(l0, inv_f), (float)qx), fadd(fmul(l1, inv_f), (float)qy), fadd(fmul(l2, inv_f), (float)qz))
-                               : mk(fadd(fdiv(l0, fs), (float)qx), fadd(fdiv(l1, fs), (float)qy), fadd(fdiv(l2, fs), (float)qz));
-            const V3 hi = pow2 ? mk(fadd(fmul(h0, inv_f), (float)qx), fadd(fmul(h1, inv_f), (float)qy), fadd(fmul(h2, inv_f), (float)qz))
-                               : mk(fadd(fdiv(h0, fs), (float)qx), fadd(fdiv(h1, fs), (float)qy), fadd(fdiv(h2, fs), (float)qz));
-            const Slab sl = ray_aabb(s, r, lo, hi);
-            if (sl.hit) {
-                o.hit = true; o.normal = sl.normal;
-                if (it != 0) o.point = sl.point;
-                o.cell[0] = qx; o.cell[1] = qy; o.cell[2] = qz;
-                o.rec = rec;
-                break;
-            }
-        }
+        if (occ && coarse_candidate(w, s, r, qx, qy, qz, __ldg(w.precords + idx), it, o)) { done = true; break; }
         bool mx, my; float t;
         dda_step(q, r, mx, my, t);
-        ++steps;
+        ++it;
     }
-    o.steps = steps;
-    o.at_exit = q;
+    if (!done && it < kMaxSteps) {
+        uint32_t idx = (uint32_t)((q.cz + 1) * w.pnxy + (q.cy + 1) * w.pnx + (q.cx + 1));
+        const int dix = r.sx, diy = r.sy * w.pnx, diz = r.sz * w.pnxy;
+        float tx = q.tx, ty = q.ty, tz = q.tz;
+        for (; it < kMaxSteps; ++it) {
+            if ((__ldg(w.ptop + (idx >> 5)) >> (idx & 31u)) & 1u) {
+                const int pz = (int)(idx / (uint32_t)w.pnxy), rem = (int)(idx - (uint32_t)pz * (uint32_t)w.pnxy);
+                const int py = rem / w.pnx, px = rem - py * w.pnx;
+                q.cx = px - 1; q.cy = py - 1; q.cz = pz - 1;
+                if (!((unsigned)q.cx < (unsigned)w.cx && (unsigned)q.cy < (unsigned)w.cy && (unsigned)q.cz < (unsigned)w.cz)) { o.oob = true; break; }
+                if (COUNT) { wk.C++; wk.K++; }
+                if (coarse_candidate(w, s, r, q.cx, q.cy, q.cz, __ldg(w.precords + idx), it, o)) break;
+            } else if (COUNT) wk.C++;
+            const bool mx = tx < ty && tx < tz;
+            const bool my = !mx && ty <= tx && ty < tz;
+            const bool mz = !mx && !my;
+            const float t = mx ? tx : (my ? ty : tz);
+            const float tn = fadd(t, mx ? r.dtx : (my ? r.dty : r.dtz));
+            tx = mx ? tn : tx; ty = my ? tn : ty; tz = mz ? tn : tz;
+            idx += (uint32_t)(mx ? dix : (my ? diy : diz));
+        }
+        q.tx = tx; q.ty = ty; q.tz = tz;
+    }
+    o.steps = it;
+    o.at_exit = q; // cell + tMax before the reference's final advance (cell valid whenever hit or oob)
 }
 
 struct FineOut {

@@ -47,7 +47,9 @@ struct vx_world {
     uint64_t nbricks = 0, occupied = 0, solid_voxels = 0;
     uint32_t words_per_brick = 16;
     uint32_t* d_top = nullptr;   // (nbricks+31)/32 words
-    uint2* d_records = nullptr;  // nbricks
+    uint2* d_records = nullptr;  // nbricks, tiled order (build-time only; freed once the padded copy exists)
+    uint32_t* d_ptop = nullptr;  // padded linear occupancy bits (traversal)
+    uint2* d_precords = nullptr; // padded linear records (traversal)
     uint32_t* d_pool = nullptr;  // occupied * words_per_brick
     float build_ms = 0.0f;
     vx::WorldView view() const {
@@ -55,6 +57,7 @@ struct vx_world {
         v.top = d_top; v.records = d_records; v.pool = d_pool;
         v.cx = (int)cx; v.cy = (int)cy; v.cz = (int)cz; v.factor = factor;
         v.words_per_brick = words_per_brick; v.tiles_x = cx / 8; v.tiles_xy = (cx / 8) * (cy / 8);
+        v.ptop = d_ptop; v.precords = d_precords; v.pnx = (int)cx + 2; v.pnxy = ((int)cx + 2) * ((int)cy + 2);
         return v;
     }
 };

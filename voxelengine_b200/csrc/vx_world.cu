@@ -219,13 +219,41 @@ __global__ void __launch_bounds__(256) compact_bricks(const uint32_t* __restrict
     *reinterpret_cast<uint4*>(pool + (uint64_t)slot * words + off) = v;
 }
 
+// ---- E: traversal layout: padded x-fastest linear grid (border bits = 1) ----------------------
+__global__ void __launch_bounds__(256) make_padded(const uint32_t* __restrict__ top, const uint2* __restrict__ records,
+                                                   uint32_t* __restrict__ ptop, uint2* __restrict__ precords, BuildGeom g, uint64_t pcells) {
+    const uint64_t wi = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; // one thread per 32-bit word of ptop
+    if (wi * 32u >= pcells) return;
+    const uint32_t pnx = g.cx + 2u, pny = g.cy + 2u, pnz = g.cz + 2u;
+    const uint32_t tW = g.cx >> 3, tH = g.cy >> 3;
+    uint32_t word = 0;
+    for (uint32_t b = 0; b < 32u; ++b) {
+        const uint64_t p = wi * 32u + b;
+        if (p >= pcells) break;
+        const uint32_t px = (uint32_t)(p % pnx), py = (uint32_t)((p / pnx) % pny), pz = (uint32_t)(p / ((uint64_t)pnx * pny));
+        uint2 rec = make_uint2(0u, 0xFFFFFFFFu);
+        bool bit = true; // border
+        if (px >= 1u && px <= g.cx && py >= 1u && py <= g.cy && pz >= 1u && pz <= g.cz && pz < pnz) {
+            const uint32_t x = px - 1u, y = py - 1u, z = pz - 1u;
+            const uint32_t t = ((x >> 3) + (y >> 3) * tW + (z >> 3) * tW * tH) * 512u + (x & 7u) + ((y & 7u) << 3) + ((z & 7u) << 6);
+            bit = (top[t >> 5] >> (t & 31u)) & 1u;
+            rec = records[t];
+        }
+        word |= (uint32_t)bit << b;
+        precords[p] = rec;
+    }
+    ptop[wi] = word;
+}
+
 // ---- export (parity) -------------------------------------------------------------------------
-__global__ void export_bricks(const uint2* __restrict__ records, const uint32_t* __restrict__ top, const uint32_t* __restrict__ pool,
-                              uint32_t words, uint32_t nbricks, uint32_t* __restrict__ brick_words, float* __restrict__ bounds6) {
+__global__ void export_bricks(const uint2* __restrict__ precords, const uint32_t* __restrict__ top, const uint32_t* __restrict__ pool,
+                              uint32_t words, uint32_t nbricks, BuildGeom g, uint32_t* __restrict__ brick_words, float* __restrict__ bounds6) {
     const uint32_t brick = blockIdx.x;
     if (brick >= nbricks) return;
     const bool occ = (top[brick >> 5] >> (brick & 31u)) & 1u;
-    const uint2 rec = records[brick];
+    uint32_t bx, by, bz;
+    brick_coords(brick, g, bx, by, bz);
+    const uint2 rec = precords[((uint64_t)(bz + 1u) * (g.cy + 2u) + (by + 1u)) * (g.cx + 2u) + (bx + 1u)];
     if (brick_words)
         for (uint32_t i = threadIdx.x; i < words; i += blockDim.x)
             brick_words[(uint64_t)brick * words + i] = occ ? pool[(uint64_t)rec.y * words + i] : 0u;
@@ -297,7 +325,14 @@ static int finish_build(vx_world* w, const uint32_t* d_tmp, const BuildGeom& g) 
     const uint64_t total_words = (uint64_t)nb * words;
     compact_bricks<<<(uint32_t)((total_words / 4 + 255) / 256), 256>>>(d_tmp, w->d_records, w->d_pool, words, total_words);
     VX_CUDA(cudaGetLastError());
+    const uint64_t pcells = (uint64_t)(w->cx + 2) * (w->cy + 2) * (w->cz + 2);
+    VX_REQUIRE(pcells < (1ull << 31), "padded coarse grid exceeds a 31-bit cell index");
+    VX_CUDA(cudaMalloc(&w->d_ptop, (size_t)((pcells + 31) / 32) * 4));
+    VX_CUDA(cudaMalloc(&w->d_precords, (size_t)pcells * sizeof(uint2)));
+    make_padded<<<(uint32_t)(((pcells + 31) / 32 + 255) / 256), 256>>>(w->d_top, w->d_records, w->d_ptop, w->d_precords, g, pcells);
+    VX_CUDA(cudaGetLastError());
     VX_CUDA(cudaDeviceSynchronize());
+    cudaFree(w->d_records); w->d_records = nullptr;
     cudaFree(d_counters);
     cudaFree(d_block_sums);
     return VX_OK;
@@ -305,7 +340,7 @@ static int finish_build(vx_world* w, const uint32_t* d_tmp, const BuildGeom& g) 
 
 static void free_world(vx_world* w) {
     if (!w) return;
-    cudaFree(w->d_top); cudaFree(w->d_records); cudaFree(w->d_pool);
+    cudaFree(w->d_top); cudaFree(w->d_records); cudaFree(w->d_pool); cudaFree(w->d_ptop); cudaFree(w->d_precords);
     delete w;
 }
 
@@ -402,7 +437,7 @@ extern "C" int vx_world_get_info(const vx_world* w, vx_world_info* info) {
     info->coarse[0] = w->cx; info->coarse[1] = w->cy; info->coarse[2] = w->cz;
     info->factor = w->factor; info->device = w->device;
     info->bricks = w->nbricks; info->occupied_bricks = w->occupied; info->solid_voxels = w->solid_voxels;
-    info->bytes_top = (w->nbricks + 31) / 32 * 4; info->bytes_records = w->nbricks * 8;
+    info->bytes_top = (w->nbricks + 31) / 32 * 4 + ((uint64_t)(w->cx + 2) * (w->cy + 2) * (w->cz + 2) + 31) / 32 * 4; info->bytes_records = (uint64_t)(w->cx + 2) * (w->cy + 2) * (w->cz + 2) * 8;
     info->bytes_pool = w->occupied * w->words_per_brick * 4;
     info->build_ms = w->build_ms;
     return VX_OK;
@@ -416,7 +451,9 @@ extern "C" int vx_world_download(const vx_world* w, uint32_t* top_words, uint32_
         uint32_t* d_bw = nullptr; float* d_b6 = nullptr;
         if (brick_words) VX_CUDA(cudaMalloc(&d_bw, (size_t)nb * w->words_per_brick * 4));
         if (bounds6) VX_CUDA(cudaMalloc(&d_b6, (size_t)nb * 24));
-        export_bricks<<<nb, 32>>>(w->d_records, w->d_top, w->d_pool, w->words_per_brick, nb, d_bw, d_b6);
+        BuildGeom g{};
+        g.cx = w->cx; g.cy = w->cy; g.cz = w->cz; g.f8 = w->factor / 8; g.tpb = g.f8 * g.f8 * g.f8;
+        export_bricks<<<nb, 32>>>(w->d_precords, w->d_top, w->d_pool, w->words_per_brick, nb, g, d_bw, d_b6);
         VX_CUDA(cudaGetLastError());
         if (brick_words) VX_CUDA(cudaMemcpy(brick_words, d_bw, (size_t)nb * w->words_per_brick * 4, cudaMemcpyDeviceToHost));
         if (bounds6) VX_CUDA(cudaMemcpy(bounds6, d_b6, (size_t)nb * 24, cudaMemcpyDeviceToHost));
