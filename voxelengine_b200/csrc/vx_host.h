@@ -40,6 +40,15 @@ struct DeviceGuard {
 } // namespace vx
 
 struct vx_world {
+    // n / d == __umulhi(n, magic) >> shift for every n < 2^31 (d >= 2): magic = ceil(2^(31+L) / d), L = ceil(log2 d),
+    // error term n * (magic*d - 2^(31+L)) < 2^31 * d <= 2^(31+L)
+    static void magic_for(uint32_t d, uint32_t& magic, uint32_t& shift) {
+        uint32_t L = 0;
+        while ((1ull << L) < d) ++L;
+        const unsigned __int128 num = (unsigned __int128)1 << (31 + L);
+        magic = (uint32_t)((num + d - 1) / d);
+        shift = L - 1;
+    }
     int device = 0;
     uint32_t X = 0, Y = 0, Z = 0;
     int factor = 8;
@@ -58,10 +67,13 @@ struct vx_world {
         v.cx = (int)cx; v.cy = (int)cy; v.cz = (int)cz; v.factor = factor;
         v.words_per_brick = words_per_brick; v.tiles_x = cx / 8; v.tiles_xy = (cx / 8) * (cy / 8);
         v.ptop = d_ptop; v.precords = d_precords; v.pnx = (int)cx + 2; v.pnxy = ((int)cx + 2) * ((int)cy + 2);
+        magic_for((uint32_t)v.pnx, v.magic_x, v.shift_x);
+        magic_for((uint32_t)v.pnxy, v.magic_xy, v.shift_xy);
         return v;
     }
 };
 
+constexpr unsigned kNextSlots = 64;
 struct vx_tracer {
     vx_world* world = nullptr;
     int device = 0;
@@ -81,4 +93,7 @@ struct vx_tracer {
     void* d_frame = nullptr; size_t frame_bytes = 0; // vx_render_host
     float tan_arg = -1.0f, tan_val = 0.0f;           // cached device tanf
     cudaStream_t stream = nullptr;
+    unsigned long long* d_next = nullptr;            // ring of ray counters for the persistent kernels
+    unsigned next_seq = 0;
+    int sm_count = 0;
 };

@@ -1,0 +1,361 @@
+// vx_march.cuh — the two-level march as a per-lane state machine driven by persistent warps.
+//
+// Same arithmetic as vx_device.cuh's primitives (VolumeRaytracer.cu:124-174, :176-352, :354-525 under IEEE
+// binary32 without contraction); what is new is the control structure:
+//   * a ray is a `Lane` record that moves between states BEGIN -> FAST/SLOW -> CAND -> (BEGIN | DONE);
+//   * a warp runs ONE loop whose body has one section per state, so lanes that are in the same state execute
+//     together no matter which ray, which coarse traversal or which phase (primary / shadow) they belong to;
+//   * finished lanes are refilled from a global ray counter (persistent warps), and a primary hit turns into its
+//     shadow ray in place;
+//   * the step counter of a coarse traversal is not carried: every step moves one cell along one axis in a fixed
+//     direction, so steps = L1 distance between the current cell and the start cell.
+#pragma once
+#include "vx_device.cuh"
+
+namespace vx {
+
+constexpr uint32_t kNoCell = 0xFFFFFFFFu;
+constexpr uint32_t kFull = 0xFFFFFFFFu;
+
+enum : uint32_t { ST_IDLE = 0, ST_BEGIN = 1, ST_FAST = 2, ST_SLOW = 3, ST_CAND = 4, ST_DONE = 5 };
+constexpr uint32_t F_ST = 7u;          // bits 0-2: state
+constexpr uint32_t F_SLOW = 1u << 3;   // traversal runs in the generic (bounds-checked, reference-ordered) mode
+constexpr uint32_t F_EDGE = 1u << 4;   // IsOnEdge at the start of this traversal (VolumeRaytracer.cu:216-232)
+constexpr uint32_t F_CAPOK = 1u << 5;  // the border is reached within kMaxSteps examinations and no tMax is NaN
+constexpr uint32_t F_HIT = 1u << 6;
+constexpr uint32_t F_SHADOW = 1u << 7; // render: this lane marches the shadow ray of its pixel
+constexpr int F_SN_SHIFT = 8;          // bits 8-10: normal code of the grid-entry clip (start_normal)
+
+// Axis-aligned unit normals as a 3-bit code: 0 = (0,0,0); 1 + 2*axis + (negative ? 1 : 0).
+__device__ __forceinline__ V3 normal_from_code(uint32_t c) {
+    const float v = (c & 1u) ? 1.0f : -1.0f; // codes 1,3,5 are positive
+    return mk((c == 1u || c == 2u) ? v : 0.0f, (c == 3u || c == 4u) ? v : 0.0f, (c == 5u || c == 6u) ? v : 0.0f);
+}
+
+struct Lane {
+    V3 d;                // normalised direction
+    float ivx, ivy, ivz; // slab inverse 1/(d == 0 ? eps : d)
+    V3 s;                // start of the current coarse traversal (brick units)
+    float tx, ty, tz;    // tMax of the current coarse traversal
+    uint32_t idx;        // bordered linear index of the current coarse cell
+    uint32_t bidx;       // ST_CAND: bordered index of the occupied cell to test (clamped cell in the generic mode)
+    uint32_t pc;         // bordered index of the previous candidate brick (VolumeRaytracer.cu:402-407) or kNoCell
+    uint32_t flags;
+    int total;           // total_steps
+    // batch planes / work counters (dead code in the render kernel unless it counts)
+    int csteps, fsteps;
+    uint32_t fcell;      // fine cell of the hit, packed 10 bits per axis
+    Work work;
+};
+
+__device__ __forceinline__ uint32_t lane_state(const Lane& L) { return L.flags & F_ST; }
+__device__ __forceinline__ void lane_set_state(Lane& L, uint32_t st) { L.flags = (L.flags & ~F_ST) | st; }
+
+__device__ __forceinline__ float lane_dt(float d, float iv) { return d != 0.0f ? fabsf(iv) : CUDART_INF_F; } // :199-201
+__device__ __forceinline__ Ray lane_ray(const Lane& L) {
+    Ray r;
+    r.d = L.d; r.ivx = L.ivx; r.ivy = L.ivy; r.ivz = L.ivz;
+    r.dtx = lane_dt(L.d.x, L.ivx); r.dty = lane_dt(L.d.y, L.ivy); r.dtz = lane_dt(L.d.z, L.ivz);
+    r.sx = L.d.x > 0.0f ? 1 : -1; r.sy = L.d.y > 0.0f ? 1 : -1; r.sz = L.d.z > 0.0f ? 1 : -1;
+    return r;
+}
+
+// bordered index <-> padded coordinates (px = x + 1, ...); divisions by the two pitches use host-made magic numbers
+__device__ __forceinline__ void cell_of(const WorldView& w, uint32_t idx, int& x, int& y, int& z) {
+    const uint32_t pz = __umulhi(idx, w.magic_xy) >> w.shift_xy;
+    const uint32_t rem = idx - pz * (uint32_t)w.pnxy;
+    const uint32_t py = __umulhi(rem, w.magic_x) >> w.shift_x;
+    x = (int)(rem - py * (uint32_t)w.pnx) - 1; y = (int)py - 1; z = (int)pz - 1;
+}
+__device__ __forceinline__ uint32_t index_of(const WorldView& w, int x, int y, int z) {
+    return (uint32_t)((z + 1) * w.pnxy + (y + 1) * w.pnx + (x + 1));
+}
+__device__ __forceinline__ bool interior(const WorldView& w, int x, int y, int z) {
+    return (unsigned)x < (unsigned)w.cx && (unsigned)y < (unsigned)w.cy && (unsigned)z < (unsigned)w.cz;
+}
+__device__ __forceinline__ int steps_from_start(const Lane& L, int x, int y, int z) {
+    return abs(x - (int)L.s.x) + abs(y - (int)L.s.y) + abs(z - (int)L.s.z);
+}
+
+// Ray set-up shared by primary, shadow and batch rays: slab inverses, grid-entry clip (VolumeRaytracer.cu:361-381).
+// `s` is origin / factor, `d` the normalised direction.
+__device__ __forceinline__ void lane_setup(const WorldView& w, Lane& L, V3 s, V3 d, uint32_t keep_flags) {
+    L.d = d;
+    L.ivx = fdiv(1.0f, d.x == 0.0f ? kFltEps : d.x);
+    L.ivy = fdiv(1.0f, d.y == 0.0f ? kFltEps : d.y);
+    L.ivz = fdiv(1.0f, d.z == 0.0f ? kFltEps : d.z);
+    uint32_t sn = 0;
+    if (!(s.x >= 0.0f && s.y >= 0.0f && s.z >= 0.0f && s.x < (float)w.cx && s.y < (float)w.cy && s.z < (float)w.cz)) {
+        const float e = (float)kEpsDDA;
+        const Ray r = lane_ray(L);
+        const Slab sl = ray_aabb(s, r, mk(e, e, e),
+                                 mk((float)((double)w.cx - kEpsDDA), (float)((double)w.cy - kEpsDDA), (float)((double)w.cz - kEpsDDA)));
+        if (sl.hit) { s = sl.point; sn = sl.ncode; }
+    }
+    L.s = s;
+    L.pc = kNoCell;
+    L.total = 0; L.csteps = 0; L.fsteps = 0; L.fcell = 0;
+    L.work.C = L.work.K = L.work.E = 0;
+    L.flags = keep_flags | (sn << F_SN_SHIFT) | ST_BEGIN;
+}
+
+// Start of one coarse DDARayTraversal (VolumeRaytracer.cu:186-232) from L.s; also the `while (total_steps <
+// maxSteps)` test of Raytrace (:383).
+__device__ __forceinline__ void lane_begin(const WorldView& w, Lane& L, int max_steps) {
+    L.flags &= ~(F_SLOW | F_EDGE | F_CAPOK);
+    if (!(L.total < max_steps)) { lane_set_state(L, ST_DONE); return; }
+    const int x0 = (int)L.s.x, y0 = (int)L.s.y, z0 = (int)L.s.z; // cvt.rzi: truncation, saturating, NaN -> 0
+    const int ox = L.d.x > 0.0f, oy = L.d.y > 0.0f, oz = L.d.z > 0.0f;
+    L.tx = L.d.x != 0.0f ? fdiv(fsub((float)(x0 + ox), L.s.x), L.d.x) : CUDART_INF_F;
+    L.ty = L.d.y != 0.0f ? fdiv(fsub((float)(y0 + oy), L.s.y), L.d.y) : CUDART_INF_F;
+    L.tz = L.d.z != 0.0f ? fdiv(fsub((float)(z0 + oz), L.s.z), L.d.z) : CUDART_INF_F;
+    // cells in [-1, dim] have a bordered index; anything else fails the first bounds test with zero steps (:283-287)
+    if (!((unsigned)(x0 + 1) <= (unsigned)(w.cx + 1) && (unsigned)(y0 + 1) <= (unsigned)(w.cy + 1) &&
+          (unsigned)(z0 + 1) <= (unsigned)(w.cz + 1))) { lane_set_state(L, ST_DONE); return; }
+    L.idx = index_of(w, x0, y0, z0);
+    const bool on_edge = x0 == w.cx || y0 == w.cy || z0 == w.cz;
+    const bool no_nan = L.tx == L.tx && L.ty == L.ty && L.tz == L.tz;
+    // examinations needed to reach the border along every axis: the fast loop carries no step counter, so the
+    // kMaxSteps cap (:236) must be unreachable before a border cell (which ends the traversal) is examined
+    const int reach = (ox ? w.cx - x0 : x0 + 1) + (oy ? w.cy - y0 : y0 + 1) + (oz ? w.cz - z0 : z0 + 1);
+    const bool capok = no_nan && reach < kMaxSteps;
+    const bool fast = capok && interior(w, x0, y0, z0);
+    L.flags |= (on_edge ? F_EDGE : 0u) | (capok ? F_CAPOK : 0u) | (fast ? 0u : F_SLOW);
+    lane_set_state(L, fast ? ST_FAST : ST_SLOW);
+}
+
+// One cell along the smallest tMax in the reference's comparison order (ties: y over x, z over both — :293-322).
+// Returns the cell after the step through (nx,ny,nz) deltas applied to idx.
+__device__ __forceinline__ void lane_step(const WorldView& w, Lane& L) {
+    const bool mx = L.tx < L.ty && L.tx < L.tz;
+    const bool my = !mx && L.ty <= L.tx && L.ty < L.tz;
+    const bool mz = !mx && !my;
+    const float t = mx ? L.tx : (my ? L.ty : L.tz);
+    const float dt = mx ? lane_dt(L.d.x, L.ivx) : (my ? lane_dt(L.d.y, L.ivy) : lane_dt(L.d.z, L.ivz));
+    const float tn = fadd(t, dt);
+    L.tx = mx ? tn : L.tx; L.ty = my ? tn : L.ty; L.tz = mz ? tn : L.tz;
+    const int dix = L.d.x > 0.0f ? 1 : -1, diy = L.d.y > 0.0f ? w.pnx : -w.pnx, diz = L.d.z > 0.0f ? w.pnxy : -w.pnxy;
+    L.idx += (uint32_t)(mx ? dix : (my ? diy : diz));
+}
+
+// Generic mode: one bounds-checked examination + step per call (the ray starts outside the grid, sits on the padded
+// far face, carries NaNs, or could reach the step cap).  Rare; exactness over speed.
+template <bool COUNT>
+__device__ __forceinline__ void lane_slow(const WorldView& w, Lane& L) {
+    int x, y, z;
+    cell_of(w, L.idx, x, y, z);
+    if ((L.flags & F_CAPOK) && interior(w, x, y, z)) { L.flags &= ~F_SLOW; lane_set_state(L, ST_FAST); return; }
+    const int it = steps_from_start(L, x, y, z);
+    const bool edge = L.flags & F_EDGE;
+    const int limx = w.cx + ((edge && L.d.x < 0.0f) ? 1 : 0), limy = w.cy + ((edge && L.d.y < 0.0f) ? 1 : 0),
+              limz = w.cz + ((edge && L.d.z < 0.0f) ? 1 : 0);
+    if (it >= kMaxSteps || !((unsigned)x < (unsigned)limx && (unsigned)y < (unsigned)limy && (unsigned)z < (unsigned)limz)) {
+        L.total += it; L.csteps += it; // cap reached or out of bounds: no hit (:236, :283-287)
+        lane_set_state(L, ST_DONE);
+        return;
+    }
+    const uint32_t b = index_of(w, min(x, w.cx - 1), min(y, w.cy - 1), min(z, w.cz - 1));
+    const bool occ = (__ldg(w.ptop + (b >> 5)) >> (b & 31u)) & 1u;
+    if (COUNT) { L.work.C++; L.work.K += occ; }
+    if (occ) { L.bidx = b; lane_set_state(L, ST_CAND); return; }
+    lane_step(w, L);
+}
+
+// Fine level: DDARayTraversal inside one brick (cells = voxels), crossing points tested against [0,factor]^3 before a
+// step is counted (VolumeRaytracer.cu:325-341).  FINE8: factor == 8, mask bit = x + 8y + 64z.
+struct FineOut {
+    bool hit, oob;
+    int steps;
+    uint32_t cell;   // packed 10 bits per axis
+    uint32_t ncode;  // normal of the last counted step
+    V3 point;
+};
+template <bool FINE8>
+__device__ __forceinline__ void fine_march(const uint32_t* __restrict__ mask, int f, V3 s, const Ray& r, FineOut& o) {
+    Dda q = dda_begin(s, r, f, f, f);
+    o.hit = false; o.oob = false; o.point = s; o.ncode = 0; o.cell = 0;
+    const uint32_t tiles = (uint32_t)f >> 3;
+    const float hi = (float)f;
+    const int ox = r.sx > 0, oy = r.sy > 0, oz = r.sz > 0;
+    int steps = 0;
+    for (int it = 0; it < kMaxSteps; ++it) {
+        if (!dda_inside(q)) { o.oob = true; break; }
+        const int qx = min(q.cx, f - 1), qy = min(q.cy, f - 1), qz = min(q.cz, f - 1);
+        const uint32_t idx = FINE8 ? (uint32_t)(qx + (qy << 3) + (qz << 6)) : tiled_index(qx, qy, qz, tiles, tiles * tiles);
+        if ((__ldg(mask + (idx >> 5)) >> (idx & 31u)) & 1u) {
+            o.hit = true; o.cell = (uint32_t)qx | ((uint32_t)qy << 10) | ((uint32_t)qz << 20);
+            break;
+        }
+        const float fx = (float)(q.cx + ox), fy = (float)(q.cy + oy), fz = (float)(q.cz + oz); // faces of the cell being left
+        bool mx, my; float t;
+        dda_step(q, r, mx, my, t);
+        const bool mz = !mx && !my;
+        const V3 p = mk(mx ? fx : fadd(s.x, fmul(t, r.d.x)), my ? fy : fadd(s.y, fmul(t, r.d.y)), mz ? fz : fadd(s.z, fmul(t, r.d.z)));
+        if (p.x < 0.0f || p.x > hi || p.y < 0.0f || p.y > hi || p.z < 0.0f || p.z > hi) { o.oob = true; break; }
+        ++steps;
+        o.point = p;
+        o.ncode = mx ? (ox ? 1u : 2u) : (my ? (oy ? 3u : 4u) : (oz ? 5u : 6u));
+    }
+    o.steps = steps;
+}
+
+// ST_CAND: the occupied cell L.bidx.  Tight-AABB slab test (VolumeRaytracer.cu:248-273); on a hit the brick is
+// marched (:409-436) and the lane either finishes (ST_DONE + F_HIT, result in pos/ncode) or re-seeds its start
+// (:438-489) and goes back to ST_BEGIN; on a slab miss it takes the step the reference takes and keeps going.
+template <bool BATCH, bool COUNT>
+__device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, uint32_t& ncode) {
+    int qx, qy, qz;
+    cell_of(w, L.bidx, qx, qy, qz);
+    int cx = qx, cy = qy, cz = qz; // traversal cell (differs from the looked-up cell only on the padded far face)
+    if (L.flags & F_SLOW) cell_of(w, L.idx, cx, cy, cz);
+    else {
+        if (!interior(w, qx, qy, qz)) { // border sentinel: the traversal left the grid (:283-287)
+            const int it = steps_from_start(L, qx, qy, qz);
+            L.total += it; L.csteps += it;
+            lane_set_state(L, ST_DONE);
+            return;
+        }
+        if (COUNT) { L.work.C++; L.work.K++; }
+    }
+    const uint2 rec = __ldg(w.precords + L.bidx);
+    const Ray r = lane_ray(L);
+    const uint32_t b = rec.x;
+    const float l0 = (float)(b & 31u), l1 = (float)((b >> 5) & 31u), l2 = (float)((b >> 10) & 31u);
+    const float h0 = (float)(((b >> 15) & 31u) + 1u), h1 = (float)(((b >> 20) & 31u) + 1u), h2 = (float)(((b >> 25) & 31u) + 1u);
+    V3 lo, hi;
+    if ((w.factor & (w.factor - 1)) == 0) { // x / 2^k == x * 2^-k exactly
+        const float inv_f = fdiv(1.0f, (float)w.factor);
+        lo = mk(fadd(fmul(l0, inv_f), (float)qx), fadd(fmul(l1, inv_f), (float)qy), fadd(fmul(l2, inv_f), (float)qz));
+        hi = mk(fadd(fmul(h0, inv_f), (float)qx), fadd(fmul(h1, inv_f), (float)qy), fadd(fmul(h2, inv_f), (float)qz));
+    } else {
+        const float fs = (float)w.factor;
+        lo = mk(fadd(fdiv(l0, fs), (float)qx), fadd(fdiv(l1, fs), (float)qy), fadd(fdiv(l2, fs), (float)qz));
+        hi = mk(fadd(fdiv(h0, fs), (float)qx), fadd(fdiv(h1, fs), (float)qy), fadd(fdiv(h2, fs), (float)qz));
+    }
+    const Slab sl = ray_aabb(L.s, r, lo, hi);
+    if (!sl.hit) {
+        lane_step(w, L);
+        lane_set_state(L, (L.flags & F_SLOW) ? ST_SLOW : ST_FAST);
+        return;
+    }
+    const int it = steps_from_start(L, cx, cy, cz);
+    const V3 point = it != 0 ? sl.point : L.s; // HitIntersectedPoint only moves `if (step != 0)` (:268-271)
+    L.total += it; L.csteps += it;
+    if (L.pc == L.bidx) { lane_set_state(L, ST_DONE); return; } // same brick as last time: give up (:402-407)
+    L.pc = L.bidx;
+    const float ff = (float)w.factor;
+    const float bx = fmul((float)qx, ff), by = fmul((float)qy, ff), bz = fmul((float)qz, ff);
+    const V3 local = mk(fsub(fmul(point.x, ff), bx), fsub(fmul(point.y, ff), by), fsub(fmul(point.z, ff), bz));
+    if (COUNT) L.work.E++;
+    FineOut q;
+    const uint32_t* mask = w.pool + (size_t)rec.y * w.words_per_brick;
+    if (w.factor == 8) fine_march<true>(mask, 8, local, r, q);
+    else fine_march<false>(mask, w.factor, local, r, q);
+    L.total += q.steps; L.fsteps += q.steps;
+    const V3 hit_pos = mk(fadd(q.point.x, bx), fadd(q.point.y, by), fadd(q.point.z, bz));
+    if (q.hit) {
+        ncode = q.steps == 0 ? sl.ncode : q.ncode;
+        pos = hit_pos;
+        if (L.total == 0) { // :515-523
+            pos = mk(fmul(L.s.x, ff), fmul(L.s.y, ff), fmul(L.s.z, ff));
+            ncode = (L.flags >> F_SN_SHIFT) & 7u;
+        }
+        if (BATCH) L.fcell = q.cell;
+        L.flags |= F_HIT;
+        lane_set_state(L, ST_DONE);
+        return;
+    }
+    V3 start = mk(fdiv(hit_pos.x, ff), fdiv(hit_pos.y, ff), fdiv(hit_pos.z, ff));
+    if (q.oob && qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) { // :438-489
+        start.x = nextafterf(start.x, L.d.x < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
+        start.y = nextafterf(start.y, L.d.y < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
+        start.z = nextafterf(start.z, L.d.z < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
+        if (qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) {
+            // NextCell of the COARSE traversal = the cell after its final advance (:347, :473)
+            const bool mx = L.tx < L.ty && L.tx < L.tz;
+            const bool my = !mx && L.ty <= L.tx && L.ty < L.tz;
+            const bool mz = !mx && !my;
+            const int nx = cx + (mx ? r.sx : 0), ny = cy + (my ? r.sy : 0), nz = cz + (mz ? r.sz : 0);
+            const float gx = fsub((float)nx, start.x), gy = fsub((float)ny, start.y), gz = fsub((float)nz, start.z);
+            const float ax = fabsf(gx), ay = fabsf(gy), az = fabsf(gz);
+            if (ax < ay && ax < az) start.x = fadd(start.x, gx);
+            else if (ay < ax && ay < az) start.y = fadd(start.y, gy);
+            else start.z = fadd(start.z, gz);
+        }
+    }
+    L.s = start;
+    lane_set_state(L, ST_BEGIN);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Warp driver.  `Policy` supplies the rays and consumes the results:
+//   uint64_t count()                      rays (ids) in this launch
+//   int max_steps()
+//   void init(w, id, L)                   set the lane up for ray `id` (lane_setup) or leave it ST_IDLE
+//   void finish(w, L, pos, ncode)         consume a finished march; may re-arm the lane (shadow ray) or set ST_IDLE
+// `next` is a zero-initialised device counter shared by all warps of the launch.
+// ---------------------------------------------------------------------------------------------
+constexpr int kChunk = 32;        // ray ids a warp draws at a time (render: one 8x4 pixel tile)
+constexpr int kRefillMin = 8;     // idle lanes that trigger a refill
+constexpr int kFastChunk = 64;    // coarse steps a lane may take before the warp looks at the other states again
+
+template <bool BATCH, bool COUNT, class Policy>
+__device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsigned long long* __restrict__ next) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const unsigned long long count = pol.count();
+    const int max_steps = pol.max_steps();
+    Lane L;
+    L.d = mk(0.0f, 0.0f, 0.0f); L.ivx = L.ivy = L.ivz = 0.0f; L.s = L.d; L.tx = L.ty = L.tz = 0.0f;
+    L.idx = 0; L.bidx = 0; L.pc = kNoCell; L.flags = ST_IDLE; L.total = 0; L.csteps = L.fsteps = 0; L.fcell = 0;
+    L.work.C = L.work.K = L.work.E = 0;
+    unsigned long long cur = 0, end = 0;
+    bool exhausted = false;
+    for (;;) {
+        V3 pos = mk(0.0f, 0.0f, 0.0f);
+        uint32_t ncode = 0;
+        if (lane_state(L) == ST_BEGIN) lane_begin(w, L, max_steps);
+        if (lane_state(L) == ST_FAST) {
+            // hot loop over the bordered linear grid: leaving the grid shows up as an occupied (border) cell
+            const float dtx = lane_dt(L.d.x, L.ivx), dty = lane_dt(L.d.y, L.ivy), dtz = lane_dt(L.d.z, L.ivz);
+            const int dix = L.d.x > 0.0f ? 1 : -1, diy = L.d.y > 0.0f ? w.pnx : -w.pnx, diz = L.d.z > 0.0f ? w.pnxy : -w.pnxy;
+            float tx = L.tx, ty = L.ty, tz = L.tz;
+            uint32_t idx = L.idx;
+            int budget = kFastChunk;
+            do {
+                if ((__ldg(w.ptop + (idx >> 5)) >> (idx & 31u)) & 1u) { lane_set_state(L, ST_CAND); break; }
+                if (COUNT) L.work.C++;
+                // no NaNs here (F_CAPOK): min axis with ties z over y over x == the reference's comparison chain
+                const float m = fminf(tx, ty);
+                const bool mz = tz <= m;
+                const bool my = !mz && ty <= tx;
+                const float tn = fadd(fminf(m, tz), mz ? dtz : (my ? dty : dtx));
+                tz = mz ? tn : tz; ty = my ? tn : ty; tx = (mz || my) ? tx : tn;
+                idx += (uint32_t)(mz ? diz : (my ? diy : dix));
+            } while (--budget);
+            L.tx = tx; L.ty = ty; L.tz = tz; L.idx = idx; L.bidx = idx;
+        }
+        if (lane_state(L) == ST_SLOW) lane_slow<COUNT>(w, L);
+        if (lane_state(L) == ST_CAND) lane_cand<BATCH, COUNT>(w, L, pos, ncode);
+        if (lane_state(L) == ST_DONE) pol.finish(w, L, pos, ncode);
+        const uint32_t idle = __ballot_sync(kFull, lane_state(L) == ST_IDLE);
+        if (idle) {
+            if (exhausted) { if (idle == kFull) break; continue; }
+            if (__popc(idle) < kRefillMin) continue;
+            if (cur == end) {
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(next, (unsigned long long)kChunk);
+                base = __shfl_sync(kFull, base, 0);
+                if (base >= count) { exhausted = true; if (idle == kFull) break; continue; }
+                cur = base; end = base + kChunk < count ? base + kChunk : count;
+            }
+            const uint32_t avail = (uint32_t)(end - cur), want = (uint32_t)__popc(idle);
+            const uint32_t take = want < avail ? want : avail;
+            const uint32_t rank = (uint32_t)__popc(idle & lt_mask);
+            if (lane_state(L) == ST_IDLE && rank < take) pol.init(w, cur + rank, L);
+            cur += take;
+        }
+    }
+}
+
+} // namespace vx

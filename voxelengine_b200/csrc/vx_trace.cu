@@ -1,9 +1,11 @@
 // vx_trace.cu — batch ray kernel, screen render kernel and their C ABI.
 //
 // Replaces the reference's `dispatch` kernel + VoxelRaytracer3D::Raytrace (VolumeRaytracer.cu:95-117,
-// :574-618) and `screenDispatch` + Graphics::RenderScreen (Renderer.cu:179-328).  The march itself
-// is vx_device.cuh.  Ray-to-thread mapping, launch shapes and buffers are new.
+// :574-618) and `screenDispatch` + Graphics::RenderScreen (Renderer.cu:179-328).  The march itself is
+// vx_march.cuh (per-lane state machine, persistent warps); this file holds the two ray sources/sinks
+// ("policies") that feed it, the launches and the C ABI.
 #include "vx_host.h"
+#include "vx_march.cuh"
 
 namespace vx {
 
@@ -12,31 +14,66 @@ struct HitPlanes {
     int32_t* coarse_steps; int32_t* fine_steps; uint32_t* counters;
 };
 
+// ---- batch rays ---------------------------------------------------------------------------------
+template <int NORM, bool COUNT>
+struct BatchPolicy {
+    const float* __restrict__ origins;
+    const float* __restrict__ dirs;
+    unsigned long long n;
+    int cap;
+    HitPlanes out;
+    unsigned long long id; // per lane: the ray being marched
+
+    __device__ __forceinline__ unsigned long long count() const { return n; }
+    __device__ __forceinline__ int max_steps() const { return cap; }
+    __device__ __forceinline__ void init(const WorldView& w, unsigned long long i, Lane& L) {
+        id = i;
+        const float ff = (float)w.factor;
+        const V3 o = mk(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]);
+        const V3 d = normalize3<NORM>(mk(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]));
+        lane_setup(w, L, mk(fdiv(o.x, ff), fdiv(o.y, ff), fdiv(o.z, ff)), d, 0u);
+    }
+    __device__ __forceinline__ void finish(const WorldView& w, Lane& L, V3 pos, uint32_t ncode) {
+        const unsigned long long i = id;
+        const bool h = L.flags & F_HIT;
+        if (out.hit) out.hit[i] = h;
+        if (out.pos) {
+            out.pos[3 * i] = h ? pos.x : CUDART_INF_F; out.pos[3 * i + 1] = h ? pos.y : CUDART_INF_F; out.pos[3 * i + 2] = h ? pos.z : CUDART_INF_F;
+        }
+        if (out.normal) {
+            const V3 nn = normal_from_code(h ? ncode : 0u);
+            out.normal[3 * i] = nn.x; out.normal[3 * i + 1] = nn.y; out.normal[3 * i + 2] = nn.z;
+        }
+        if (out.steps) out.steps[i] = L.total;
+        if (out.voxel || out.brick) {
+            int bx = 0, by = 0, bz = 0;
+            if (h) cell_of(w, L.pc, bx, by, bz);
+            if (out.voxel) {
+                out.voxel[3 * i] = h ? bx * w.factor + (int)(L.fcell & 1023u) : -1;
+                out.voxel[3 * i + 1] = h ? by * w.factor + (int)((L.fcell >> 10) & 1023u) : -1;
+                out.voxel[3 * i + 2] = h ? bz * w.factor + (int)((L.fcell >> 20) & 1023u) : -1;
+            }
+            if (out.brick) out.brick[i] = h ? tiled_index(bx, by, bz, w.tiles_x, w.tiles_xy) : 0xFFFFFFFFu;
+        }
+        if (out.coarse_steps) out.coarse_steps[i] = L.csteps;
+        if (out.fine_steps) out.fine_steps[i] = L.fsteps;
+        if (COUNT && out.counters) { out.counters[3 * i] = L.work.C; out.counters[3 * i + 1] = L.work.K; out.counters[3 * i + 2] = L.work.E; }
+        L.flags = ST_IDLE;
+    }
+};
+
 template <int NORM, bool COUNT>
 __global__ void __launch_bounds__(128) trace_rays(WorldView w, const float* __restrict__ origins, const float* __restrict__ dirs,
-                                                  size_t n, int max_steps, HitPlanes out) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const V3 o = mk(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]);
-    const V3 d = mk(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
-    MarchOut m;
-    const bool h = march<NORM, COUNT>(w, o, d, max_steps, m);
-    if (out.hit) out.hit[i] = h;
-    if (out.pos) {
-        out.pos[3 * i] = h ? m.pos.x : CUDART_INF_F; out.pos[3 * i + 1] = h ? m.pos.y : CUDART_INF_F; out.pos[3 * i + 2] = h ? m.pos.z : CUDART_INF_F;
-    }
-    if (out.normal) { out.normal[3 * i] = m.normal.x; out.normal[3 * i + 1] = m.normal.y; out.normal[3 * i + 2] = m.normal.z; }
-    if (out.steps) out.steps[i] = m.steps;
-    if (out.voxel) { out.voxel[3 * i] = m.voxel[0]; out.voxel[3 * i + 1] = m.voxel[1]; out.voxel[3 * i + 2] = m.voxel[2]; }
-    if (out.brick) out.brick[i] = m.brick;
-    if (out.coarse_steps) out.coarse_steps[i] = m.coarse_steps;
-    if (out.fine_steps) out.fine_steps[i] = m.fine_steps;
-    if (COUNT && out.counters) { out.counters[3 * i] = m.work.C; out.counters[3 * i + 1] = m.work.K; out.counters[3 * i + 2] = m.work.E; }
+                                                  unsigned long long n, int max_steps, HitPlanes out, unsigned long long* next) {
+    BatchPolicy<NORM, COUNT> pol;
+    pol.origins = origins; pol.dirs = dirs; pol.n = n; pol.cap = max_steps; pol.out = out; pol.id = 0;
+    run_lanes<true, COUNT>(w, pol, next);
 }
 
 // ---- screen ----------------------------------------------------------------------------------
 struct FrameParams {
     V3 origin, fwd, up, right;
+    V3 start0;                 // origin / factor (IEEE division, done once on the host)
     V3 light, light_color, ambient;
     float tan_half;
     uint32_t W, H;
@@ -44,6 +81,8 @@ struct FrameParams {
     int checkerboard, debug_view, shadows, crosshair;
     uint32_t tx0, ty0, tw, th; // thread-space rectangle
     uint32_t band_count, band_index; // multi-GPU: 8-row bands dealt round-robin, this launch renders bands == index (mod count)
+    uint32_t mcols;            // 16x8 macro tiles per band
+    unsigned long long ids;    // ray ids of this launch = mcols * my_bands * 128
 };
 
 __device__ __forceinline__ void put_pixel(uint8_t* __restrict__ bgra, uint32_t W, uint32_t H, int x, int y, V3 c) {
@@ -54,22 +93,9 @@ __device__ __forceinline__ void put_pixel(uint8_t* __restrict__ bgra, uint32_t W
     reinterpret_cast<uint32_t*>(bgra)[(size_t)y * W + x] = b | (g << 8) | (r << 16) | 0xFF000000u;
 }
 
-struct ShadowInfo { bool cast, hit; Work work; };
-
-template <int NORM, bool COUNT>
-__device__ __forceinline__ V3 shade(const WorldView& w, const FrameParams& f, V3 n, V3 pos, int& extra_steps, ShadowInfo& si) {
-    // calculateColor, Renderer.cu:90-168 (AO block: samples = 0, no-op)
-    extra_steps = 0;
-    const V3 sray = normalize3<NORM>(f.light);
-    const V3 spos = mk(fadd(pos.x, fmul(sray.x, 0.01f)), fadd(pos.y, fmul(sray.y, 0.01f)), fadd(pos.z, fmul(sray.z, 0.01f)));
-    bool shadowed = false;
-    si.cast = false; si.hit = false; si.work.C = si.work.K = si.work.E = 0;
-    if (f.shadows) {
-        MarchOut m;
-        shadowed = march<NORM, COUNT>(w, spos, sray, kMaxSteps, m);
-        extra_steps += m.steps;
-        si.cast = true; si.hit = shadowed; si.work = m.work;
-    }
+// calculateColor, Renderer.cu:90-168 (AO block: samples = 0, no-op) with the shadow result supplied, then Tonemap (:170-177)
+template <int NORM>
+__device__ __forceinline__ V3 shade(const FrameParams& f, V3 n, V3 pos, bool shadowed) {
     const float nl = dot3(n, f.light);
     const float ldot = fmul(fmaxf(nl, 0.0f), shadowed ? 0.0f : 1.0f);
     const float up_dot = dot3(n, mk(0.0f, 1.0f, 0.0f));
@@ -84,81 +110,127 @@ __device__ __forceinline__ V3 shade(const WorldView& w, const FrameParams& f, V3
         const float spec = powf(fmaxf(dot3(view, refl), 0.0f), 32.0f);
         c = mk(fadd(c.x, fmul(spec, f.light_color.x)), fadd(c.y, fmul(spec, f.light_color.y)), fadd(c.z, fmul(spec, f.light_color.z)));
     }
-    return c;
+    return mk(fdiv(c.x, fadd(c.x, 1.0f)), fdiv(c.y, fadd(c.y, 1.0f)), fdiv(c.z, fadd(c.z, 1.0f)));
 }
 
-// One thread per reference thread coordinate (tx,ty); a warp covers an 8x4 block of thread
-// coordinates instead of the reference's 32x1 strip (coherence), results are identical.
+// Ray id -> pixel: ids are dealt in 8x4 tiles (32 consecutive ids), four tiles forming a 16x8 macro tile, macro tiles
+// row-major inside this launch's bands.  Pixel (thread) coordinates and the written image are the reference's.
 //
-// STATS: accumulate per-frame ray/step/work counters into `stats` (8 x uint64: primary rays,
-// primary hits, shadow rays, shadow hits, steps, C, K, E — SURVEY.md §8d) with one atomic per warp.
+// STATS: per-frame counters (8 x uint64: primary rays, primary hits, shadow rays, shadow hits, steps, C, K, E —
+// SURVEY.md §8d), added with one atomic per group of lanes finishing together.
+template <int NORM, bool STATS>
+struct RenderPolicy {
+    const FrameParams& f;
+    uint8_t* __restrict__ bgra;
+    int32_t* __restrict__ steps_plane;
+    unsigned long long* __restrict__ stats;
+    // per lane
+    uint32_t pix;   // x | y << 15 | crosshair thread << 30
+    V3 ppos;        // primary hit (while the shadow ray marches)
+    uint32_t pn;    // primary normal code
+    int psteps;
+    Work pwork;
+
+    __device__ __forceinline__ RenderPolicy(const FrameParams& fp, uint8_t* b, int32_t* sp, unsigned long long* st)
+        : f(fp), bgra(b), steps_plane(sp), stats(st), pix(0), pn(0), psteps(0) { ppos = mk(0.0f, 0.0f, 0.0f); pwork.C = pwork.K = pwork.E = 0; }
+    __device__ __forceinline__ unsigned long long count() const { return f.ids; }
+    __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
+
+    // getRayDirection, Renderer.cu:44-59
+    __device__ __forceinline__ V3 primary_dir(int x, int y) const {
+        const int W = (int)f.W, H = (int)f.H;
+        const float u = fsub(fmul(fdiv((float)x, (float)W), 2.0f), 1.0f), v = fsub(fmul(fdiv((float)y, (float)H), 2.0f), 1.0f);
+        const float aspect = fdiv((float)W, (float)H);
+        const float a = fmul(u, fmul(f.tan_half, aspect)), b = fmul(v, f.tan_half);
+        const V3 rd = mk(fadd(fadd(f.fwd.x, fmul(a, f.right.x)), fmul(b, f.up.x)), fadd(fadd(f.fwd.y, fmul(a, f.right.y)), fmul(b, f.up.y)),
+                         fadd(fadd(f.fwd.z, fmul(a, f.right.z)), fmul(b, f.up.z)));
+        return normalize3<NORM>(rd);
+    }
+
+    __device__ __forceinline__ void init(const WorldView& w, unsigned long long id64, Lane& L) {
+        const uint32_t id = (uint32_t)id64;
+        const uint32_t j = id & 31u, k = (id >> 5) & 3u, macro = id >> 7;
+        const uint32_t lband = macro / f.mcols, mcol = macro - lband * f.mcols;
+        const uint32_t tx = f.tx0 + mcol * 16u + (k & 1u) * 8u + (j & 7u);
+        const uint32_t ty = f.ty0 + (lband * f.band_count + f.band_index) * 8u + (k >> 1) * 4u + (j >> 3);
+        if (tx >= f.tx0 + f.tw || ty >= f.ty0 + f.th) return;
+        int x = (int)tx, y = (int)ty;
+        if (f.checkerboard) { // Renderer.cu:186-194
+            y *= 2;
+            if ((x % 2) == 0) y += 1;
+            if (f.frame_number % 2u == 0u) y += 1;
+        }
+        if ((uint32_t)x >= f.W || (uint32_t)y >= f.H) return;
+        pix = (uint32_t)x | ((uint32_t)y << 15) | ((f.crosshair && tx == (f.W >> 1) && ty == (f.H >> 1)) ? (1u << 30) : 0u);
+        // Raytrace normalises the (already normalised) direction it is given once more (VolumeRaytracer.cu:363)
+        lane_setup(w, L, f.start0, normalize3<NORM>(primary_dir(x, y)), 0u);
+    }
+
+    __device__ __forceinline__ void finish(const WorldView& w, Lane& L, V3 pos, uint32_t ncode) {
+        const bool hit = L.flags & F_HIT;
+        bool phit, cast = false, shadowed = false;
+        int steps;
+        Work wk = L.work;
+        if (!(L.flags & F_SHADOW)) {
+            phit = hit;
+            steps = L.total;
+            if (hit && !f.debug_view && f.shadows) { // the shadow Raytrace of Renderer.cu:102: this lane becomes the shadow ray
+                ppos = pos; pn = ncode; psteps = L.total;
+                if (STATS) pwork = L.work;
+                const V3 sray = normalize3<NORM>(f.light);
+                const float ff = (float)w.factor;
+                const V3 so = mk(fadd(pos.x, fmul(sray.x, 0.01f)), fadd(pos.y, fmul(sray.y, 0.01f)), fadd(pos.z, fmul(sray.z, 0.01f)));
+                lane_setup(w, L, mk(fdiv(so.x, ff), fdiv(so.y, ff), fdiv(so.z, ff)), normalize3<NORM>(sray), F_SHADOW);
+                return;
+            }
+        } else {
+            phit = true; cast = true; shadowed = hit;
+            steps = psteps + L.total;
+            pos = ppos; ncode = pn;
+            if (STATS) { wk.C += pwork.C; wk.K += pwork.K; wk.E += pwork.E; }
+        }
+        const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
+        const int W = (int)f.W, H = (int)f.H;
+        if (phit) {
+            const V3 nn = normal_from_code(ncode);
+            const V3 n = mk(-nn.x, -nn.y, -nn.z);
+            if (f.debug_view) { // Renderer.cu:215-243
+                const V3 dl = mk(fsub(pos.x, f.origin.x), fsub(pos.y, f.origin.y), fsub(pos.z, f.origin.z));
+                const float dist = __fsqrt_rn(dot3(dl, dl));
+                const float md = (float)(1.0 + kEpsDDA);
+                const V3 hp = mk(fmodf(fdiv(pos.x, 128.0f), md), fmodf(fdiv(pos.y, 128.0f), md), fmodf(fdiv(pos.z, 128.0f), md));
+                if (x < (W >> 1) && y < (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, n);
+                else if (x >= (W >> 1) && y < (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, hp);
+                else if (x < (W >> 1)) {}
+                else put_pixel(bgra, f.W, f.H, x, y, mk(fmul(dist, 0.01f), 0.0f, 0.0f));
+            } else {
+                put_pixel(bgra, f.W, f.H, x, y, shade<NORM>(f, n, pos, shadowed));
+            }
+        } else {
+            put_pixel(bgra, f.W, f.H, x, y, primary_dir(x, y)); // miss: colour = ray direction, Renderer.cu:254-258
+        }
+        if (pix & (1u << 30)) put_pixel(bgra, f.W, f.H, x, y, mk(10.0f, 10.0f, 10.0f)); // crosshair, :260-268
+        if (f.debug_view && x < (W >> 1) && y > (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(fdiv((float)steps, 256.0f), 0.0f, 0.0f));
+        if (steps_plane) steps_plane[(size_t)y * f.W + x] = steps;
+        if (STATS) {
+            const uint32_t m = __activemask();
+            const uint32_t leader = (uint32_t)__ffs((int)m) - 1u, lane = threadIdx.x & 31u;
+            const uint32_t v[8] = {1u, (uint32_t)phit, (uint32_t)cast, (uint32_t)shadowed, (uint32_t)steps, wk.C, wk.K, wk.E};
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const uint32_t sum = __reduce_add_sync(m, v[k]);
+                if (lane == leader && sum) atomicAdd(stats + k, (unsigned long long)sum);
+            }
+        }
+        L.flags = ST_IDLE;
+    }
+};
+
 template <int NORM, bool STATS>
 __global__ void __launch_bounds__(128) render_frame(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
-                                                    unsigned long long* __restrict__ stats) {
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    // block = 4 warps = 16x8 thread coordinates; warp = 8x4
-    const uint32_t tx = f.tx0 + blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
-    const uint32_t ty = f.ty0 + (blockIdx.y * f.band_count + f.band_index) * 8u + (warp >> 1) * 4u + (lane >> 3);
-    unsigned long long st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    bool live = !(tx >= f.tx0 + f.tw || ty >= f.ty0 + f.th);
-    int x = (int)tx, y = (int)ty;
-    if (f.checkerboard) { // Renderer.cu:186-194
-        y *= 2;
-        if ((x % 2) == 0) y += 1;
-        if (f.frame_number % 2u == 0u) y += 1;
-    }
-    live = live && !((uint32_t)x >= f.W || (uint32_t)y >= f.H);
-    if (!STATS && !live) return;
-    if (live) {
-    const int W = (int)f.W, H = (int)f.H;
-    // getRayDirection, Renderer.cu:44-59
-    const float u = fsub(fmul(fdiv((float)x, (float)W), 2.0f), 1.0f), v = fsub(fmul(fdiv((float)y, (float)H), 2.0f), 1.0f);
-    const float aspect = fdiv((float)W, (float)H);
-    const float a = fmul(u, fmul(f.tan_half, aspect)), b = fmul(v, f.tan_half);
-    V3 rd = mk(fadd(fadd(f.fwd.x, fmul(a, f.right.x)), fmul(b, f.up.x)), fadd(fadd(f.fwd.y, fmul(a, f.right.y)), fmul(b, f.up.y)),
-               fadd(fadd(f.fwd.z, fmul(a, f.right.z)), fmul(b, f.up.z)));
-    rd = normalize3<NORM>(rd);
-    MarchOut m;
-    const bool hit = march<NORM, STATS>(w, f.origin, rd, kMaxSteps, m);
-    int steps = m.steps;
-    if (STATS) { st[0] = 1; st[1] = hit; st[5] = m.work.C; st[6] = m.work.K; st[7] = m.work.E; }
-    const V3 n = mk(-m.normal.x, -m.normal.y, -m.normal.z);
-    if (hit) {
-        if (f.debug_view) { // Renderer.cu:215-243
-            const V3 dl = mk(fsub(m.pos.x, f.origin.x), fsub(m.pos.y, f.origin.y), fsub(m.pos.z, f.origin.z));
-            const float dist = __fsqrt_rn(dot3(dl, dl));
-            const float md = (float)(1.0 + kEpsDDA);
-            const V3 hp = mk(fmodf(fdiv(m.pos.x, 128.0f), md), fmodf(fdiv(m.pos.y, 128.0f), md), fmodf(fdiv(m.pos.z, 128.0f), md));
-            if (x < (W >> 1) && y < (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, n);
-            else if (x >= (W >> 1) && y < (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, hp);
-            else if (x < (W >> 1)) {}
-            else put_pixel(bgra, f.W, f.H, x, y, mk(fmul(dist, 0.01f), 0.0f, 0.0f));
-        } else {
-            int extra = 0;
-            ShadowInfo si;
-            V3 c = shade<NORM, STATS>(w, f, n, m.pos, extra, si);
-            if (STATS) { st[2] = si.cast; st[3] = si.hit; st[5] += si.work.C; st[6] += si.work.K; st[7] += si.work.E; }
-            c = mk(fdiv(c.x, fadd(c.x, 1.0f)), fdiv(c.y, fadd(c.y, 1.0f)), fdiv(c.z, fadd(c.z, 1.0f))); // Tonemap, Renderer.cu:170-177
-            steps += extra;
-            put_pixel(bgra, f.W, f.H, x, y, c);
-        }
-    } else {
-        put_pixel(bgra, f.W, f.H, x, y, rd); // Renderer.cu:254-258
-    }
-    if (f.crosshair && tx == (f.W >> 1) && ty == (f.H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(10.0f, 10.0f, 10.0f));
-    if (f.debug_view && x < (W >> 1) && y > (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(fdiv((float)steps, 256.0f), 0.0f, 0.0f));
-    if (steps_plane) steps_plane[(size_t)y * f.W + x] = steps;
-    if (STATS) st[4] = (unsigned long long)steps;
-    } // live
-    if (STATS) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            unsigned long long v = st[k];
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
-            if (lane == 0 && v) atomicAdd(stats + k, v);
-        }
-    }
+                                                    unsigned long long* __restrict__ stats, unsigned long long* next) {
+    RenderPolicy<NORM, STATS> pol(f, bgra, steps_plane, stats);
+    run_lanes<false, STATS>(w, pol, next);
 }
 
 __global__ void tanf_kernel(float x, float* out) { *out = tanf(x); }
@@ -189,7 +261,9 @@ extern "C" int vx_tracer_create(vx_tracer** out, vx_world* w, size_t max_rays) {
     VX_ALLOC(t->d_hit, n); VX_ALLOC(t->d_pos, n * 12); VX_ALLOC(t->d_normal, n * 12); VX_ALLOC(t->d_steps, n * 4);
     VX_ALLOC(t->d_voxel, n * 12); VX_ALLOC(t->d_brick, n * 4); VX_ALLOC(t->d_csteps, n * 4); VX_ALLOC(t->d_fsteps, n * 4);
     VX_ALLOC(t->d_counters, n * 12);
+    VX_ALLOC(t->d_next, kNextSlots * sizeof(unsigned long long));
 #undef VX_ALLOC
+    cudaDeviceGetAttribute(&t->sm_count, cudaDevAttrMultiProcessorCount, t->device);
     VX_CUDA(cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking));
     *out = t;
     return VX_OK;
@@ -200,9 +274,29 @@ extern "C" int vx_tracer_destroy(vx_tracer* t) {
     DeviceGuard guard(t->device);
     cudaFree(t->d_origins); cudaFree(t->d_dirs); cudaFree(t->d_hit); cudaFree(t->d_pos); cudaFree(t->d_normal);
     cudaFree(t->d_steps); cudaFree(t->d_voxel); cudaFree(t->d_brick); cudaFree(t->d_csteps); cudaFree(t->d_fsteps);
-    cudaFree(t->d_counters); cudaFree(t->d_frame);
+    cudaFree(t->d_counters); cudaFree(t->d_frame); cudaFree(t->d_next);
     if (t->stream) cudaStreamDestroy(t->stream);
     delete t;
+    return VX_OK;
+}
+
+// Persistent launch: as many 128-thread blocks as stay resident (or fewer when there is less work), plus a fresh
+// zeroed ray counter taken from a small ring so launches on different streams do not share one.
+template <class K>
+static int persistent_blocks(vx_tracer* t, K kernel, unsigned long long ids, unsigned& blocks) {
+    int per_sm = 0;
+    VX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 128, 0));
+    if (per_sm < 1) per_sm = 1;
+    const unsigned long long full = (unsigned long long)per_sm * (unsigned long long)(t->sm_count > 0 ? t->sm_count : 148);
+    const unsigned long long need = (ids + 127) / 128;
+    blocks = (unsigned)(need < full ? need : full);
+    if (blocks == 0) blocks = 1;
+    return VX_OK;
+}
+static int next_counter(vx_tracer* t, cudaStream_t s, unsigned long long** out) {
+    unsigned long long* p = t->d_next + (t->next_seq++ % kNextSlots);
+    VX_CUDA(cudaMemsetAsync(p, 0, sizeof(unsigned long long), s));
+    *out = p;
     return VX_OK;
 }
 
@@ -214,9 +308,13 @@ static int launch_trace(vx_tracer* t, const float* d_o, const float* d_d, size_t
     VX_REQUIRE(norm >= 0 && norm <= 2, "bad norm_mode");
     HitPlanes p{out->hit, out->pos, out->normal, out->steps, out->voxel, out->brick, out->coarse_steps, out->fine_steps, out->counters};
     const WorldView w = t->world->view();
-    const unsigned blocks = (unsigned)((n + 127) / 128);
     const bool count = out->counters != nullptr;
-#define VX_LAUNCH(N, C) trace_rays<N, C><<<blocks, 128, 0, s>>>(w, d_o, d_d, n, max_steps, p)
+    unsigned long long* next = nullptr;
+    int rc = next_counter(t, s, &next);
+    if (rc) return rc;
+    unsigned blocks = 1;
+#define VX_LAUNCH(N, C) do { rc = persistent_blocks(t, trace_rays<N, C>, n, blocks); if (rc) return rc; \
+        trace_rays<N, C><<<blocks, 128, 0, s>>>(w, d_o, d_d, (unsigned long long)n, max_steps, p, next); } while (0)
     if (count) { if (norm == 0) VX_LAUNCH(0, true); else if (norm == 1) VX_LAUNCH(1, true); else VX_LAUNCH(2, true); }
     else { if (norm == 0) VX_LAUNCH(0, false); else if (norm == 1) VX_LAUNCH(1, false); else VX_LAUNCH(2, false); }
 #undef VX_LAUNCH
@@ -309,7 +407,10 @@ extern "C" int vx_device_normalize(const float* dirs, float* out, size_t n, int 
 
 static int fill_frame(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* o, uint32_t W, uint32_t H, FrameParams& f) {
     VX_REQUIRE(W > 0 && H > 0, "empty frame");
+    VX_REQUIRE(W < 32768 && H < 32768, "frame dimensions must be below 32768");
     f.origin = V3{cam->origin[0], cam->origin[1], cam->origin[2]};
+    const float ff = (float)t->world->factor;
+    f.start0 = V3{cam->origin[0] / ff, cam->origin[1] / ff, cam->origin[2] / ff}; // start = origin / factor, VolumeRaytracer.cu:361
     f.fwd = V3{cam->fwd[0], cam->fwd[1], cam->fwd[2]};
     f.up = V3{cam->up[0], cam->up[1], cam->up[2]};
     f.right = V3{cam->right[0], cam->right[1], cam->right[2]};
@@ -356,17 +457,21 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     const uint32_t bands = (f.th + 7u) / 8u;
     const uint32_t my_bands = bands > f.band_index ? (bands - f.band_index + f.band_count - 1u) / f.band_count : 0u;
     if (my_bands == 0) return VX_OK;
-    const dim3 grid((f.tw + 15u) / 16u, my_bands);
+    f.mcols = (f.tw + 15u) / 16u;
+    f.ids = (unsigned long long)f.mcols * my_bands * 128ull;
+    VX_REQUIRE(f.ids < (1ull << 32), "frame too large for one launch");
     const WorldView w = t->world->view();
     unsigned long long* st = (unsigned long long*)opts->d_stats;
     cudaStream_t cs = (cudaStream_t)stream;
-    if (opts->norm_mode == VX_NORM_HOST) {
-        if (st) render_frame<1, true><<<grid, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st);
-        else render_frame<1, false><<<grid, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, nullptr);
-    } else {
-        if (st) render_frame<0, true><<<grid, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st);
-        else render_frame<0, false><<<grid, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, nullptr);
-    }
+    unsigned long long* next = nullptr;
+    rc = next_counter(t, cs, &next);
+    if (rc) return rc;
+    unsigned blocks = 1;
+#define VX_LAUNCH(N, S) do { rc = persistent_blocks(t, render_frame<N, S>, f.ids, blocks); if (rc) return rc; \
+        render_frame<N, S><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, next); } while (0)
+    if (opts->norm_mode == VX_NORM_HOST) { if (st) VX_LAUNCH(1, true); else VX_LAUNCH(1, false); }
+    else { if (st) VX_LAUNCH(0, true); else VX_LAUNCH(0, false); }
+#undef VX_LAUNCH
     VX_CUDA(cudaGetLastError());
     return VX_OK;
 }
