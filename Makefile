@@ -5,7 +5,7 @@ NVFLAGS := -std=c++17 -O3 $(ARCH) -lineinfo -fmad=false -Xcompiler -fPIC -Xptxas
 CSRC   := voxelengine_b200/csrc
 LIB    := voxelengine_b200/lib/libvxrt.so
 SRCS   := $(CSRC)/vx_world.cu $(CSRC)/vx_trace.cu
-HDRS   := $(CSRC)/vx_device.cuh $(CSRC)/vx_noise.cuh $(CSRC)/vx_host.h include/vxrt.h
+HDRS   := $(CSRC)/vx_device.cuh $(CSRC)/vx_march.cuh $(CSRC)/vx_noise.cuh $(CSRC)/vx_host.h include/vxrt.h
 
 all: $(LIB)
 

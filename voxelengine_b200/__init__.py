@@ -17,7 +17,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libvxrt.so")
+LIB_PATH = os.environ.get("VXRT_LIB") or os.path.join(_HERE, "lib", "libvxrt.so")  # VXRT_LIB: tuning builds (tools/)
 
 NORM_DEVICE, NORM_HOST, NORM_NONE = 0, 1, 2
 MAX_STEPS = 2048

@@ -287,17 +287,55 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
     lane_set_state(L, ST_BEGIN);
 }
 
+// Occupancy bit of bordered cell idx; the AND and the compare are one LOP3 with a predicate result.
+__device__ __forceinline__ bool cell_bit(const uint32_t* __restrict__ bits, uint32_t idx) {
+    const uint32_t word = __ldg(bits + (idx >> 5));
+    uint32_t p;
+    asm("{\n\t.reg .pred q;\n\t.reg .b32 t, u;\n\t"
+        "shf.r.wrap.b32 t, %1, 0, %2;\n\t"
+        "lop3.or.b32 u|q, t, 1, 0, 0xC0, 0;\n\t" // u = t & 1; q = (u != 0)
+        "selp.u32 %0, 1, 0, q;\n\t}" : "=r"(p) : "r"(word), "r"(idx));
+    return p != 0u;
+}
+
+// One fast-loop step.  With no NaN among the tMax values (F_CAPOK) the reference's comparison chain (:293-322) picks the
+// axis of the minimum with ties z over y over x, and the chosen axis' tMax IS that minimum, so "tMax[axis] += tDelta[axis]"
+// under the axis predicate is the reference's add.  Written as predicated adds (FMA pipe) because the select-based form
+// the compiler prefers is bound by the half-rate ALU pipe (profiles/).
+__device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint32_t& idx, float dtx, float dty, float dtz, int dix, int diy,
+                                          int diz) {
+    asm("{\n\t.reg .pred pz, py, px;\n\t.reg .f32 m;\n\t"
+        "min.f32 m, %0, %1;\n\t"
+        "setp.le.f32 pz, %2, m;\n\t"
+        "setp.le.and.f32 py, %1, %0, !pz;\n\t"
+        "setp.gt.and.f32 px, %1, %0, !pz;\n\t"
+        "@pz add.rn.f32 %2, %2, %6;\n\t"
+        "@py add.rn.f32 %1, %1, %5;\n\t"
+        "@px add.rn.f32 %0, %0, %4;\n\t"
+        "@pz add.s32 %3, %3, %9;\n\t"
+        "@py add.s32 %3, %3, %8;\n\t"
+        "@px add.s32 %3, %3, %7;\n\t}"
+        : "+f"(tx), "+f"(ty), "+f"(tz), "+r"(idx)
+        : "f"(dtx), "f"(dty), "f"(dtz), "r"(dix), "r"(diy), "r"(diz));
+}
+
 // ---------------------------------------------------------------------------------------------
 // Warp driver.  `Policy` supplies the rays and consumes the results:
 //   uint64_t count()                      rays (ids) in this launch
 //   int max_steps()
 //   void init(w, id, L)                   set the lane up for ray `id` (lane_setup) or leave it ST_IDLE
-//   void finish(w, L, pos, ncode)         consume a finished march; may re-arm the lane (shadow ray) or set ST_IDLE
+//   void finish(w, L, pos, ncode)         consume a finished march and set the lane ST_IDLE (or re-arm it)
+//   kRefill                               idle lanes that trigger a refill (32: whole tiles only)
 // `next` is a zero-initialised device counter shared by all warps of the launch.
 // ---------------------------------------------------------------------------------------------
-constexpr int kChunk = 32;        // ray ids a warp draws at a time (render: one 8x4 pixel tile)
-constexpr int kRefillMin = 8;     // idle lanes that trigger a refill
-constexpr int kFastChunk = 64;    // coarse steps a lane may take before the warp looks at the other states again
+#ifndef VX_REFILL_MIN
+#define VX_REFILL_MIN 8
+#endif
+#ifndef VX_FAST_CHUNK
+#define VX_FAST_CHUNK 64
+#endif
+constexpr int kChunk = 32;                  // ray ids a warp draws at a time (render: one 8x4 pixel tile)
+constexpr int kFastChunk = VX_FAST_CHUNK;   // coarse steps a lane may take before the warp looks at the other states again
 
 template <bool BATCH, bool COUNT, class Policy>
 __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsigned long long* __restrict__ next) {
@@ -322,16 +360,11 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
             float tx = L.tx, ty = L.ty, tz = L.tz;
             uint32_t idx = L.idx;
             int budget = kFastChunk;
+#pragma unroll 4
             do {
-                if ((__ldg(w.ptop + (idx >> 5)) >> (idx & 31u)) & 1u) { lane_set_state(L, ST_CAND); break; }
+                if (cell_bit(w.ptop, idx)) { lane_set_state(L, ST_CAND); break; }
                 if (COUNT) L.work.C++;
-                // no NaNs here (F_CAPOK): min axis with ties z over y over x == the reference's comparison chain
-                const float m = fminf(tx, ty);
-                const bool mz = tz <= m;
-                const bool my = !mz && ty <= tx;
-                const float tn = fadd(fminf(m, tz), mz ? dtz : (my ? dty : dtx));
-                tz = mz ? tn : tz; ty = my ? tn : ty; tx = (mz || my) ? tx : tn;
-                idx += (uint32_t)(mz ? diz : (my ? diy : dix));
+                fast_step(tx, ty, tz, idx, dtx, dty, dtz, dix, diy, diz);
             } while (--budget);
             L.tx = tx; L.ty = ty; L.tz = tz; L.idx = idx; L.bidx = idx;
         }
@@ -341,7 +374,7 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
         const uint32_t idle = __ballot_sync(kFull, lane_state(L) == ST_IDLE);
         if (idle) {
             if (exhausted) { if (idle == kFull) break; continue; }
-            if (__popc(idle) < kRefillMin) continue;
+            if (__popc(idle) < Policy::kRefill) continue;
             if (cur == end) {
                 unsigned long long base = 0;
                 if (lane == 0) base = atomicAdd(next, (unsigned long long)kChunk);

@@ -23,6 +23,7 @@ struct BatchPolicy {
     int cap;
     HitPlanes out;
     unsigned long long id; // per lane: the ray being marched
+    static constexpr int kRefill = VX_REFILL_MIN;
 
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return cap; }
@@ -113,26 +114,77 @@ __device__ __forceinline__ V3 shade(const FrameParams& f, V3 n, V3 pos, bool sha
     return mk(fdiv(c.x, fadd(c.x, 1.0f)), fdiv(c.y, fadd(c.y, 1.0f)), fdiv(c.z, fadd(c.z, 1.0f)));
 }
 
-// Ray id -> pixel: ids are dealt in 8x4 tiles (32 consecutive ids), four tiles forming a 16x8 macro tile, macro tiles
-// row-major inside this launch's bands.  Pixel (thread) coordinates and the written image are the reference's.
+// A frame is two launches:
+//   primary_rays : persistent warps, one 8x4 pixel tile per refill (coherent rays).  A miss writes its pixel; a hit
+//                  is either shaded at once (shadows off / debug view) or appended to the frame's shadow queue.
+//   shadow_rays  : persistent warps pull queue entries (neighbouring pixels sit next to each other in the queue) and
+//                  refill finished lanes in groups, because about half of the sun rays end after a few steps while
+//                  the rest cross the whole grid; the pixel is shaded and written when its shadow ray ends.
+// Ray id -> pixel for the primary launch: ids are dealt in 8x4 tiles (32 consecutive ids), four tiles forming a
+// 16x8 macro tile, macro tiles row-major inside this launch's bands.  Pixel (thread) coordinates and the written
+// image are the reference's.
 //
 // STATS: per-frame counters (8 x uint64: primary rays, primary hits, shadow rays, shadow hits, steps, C, K, E —
 // SURVEY.md §8d), added with one atomic per group of lanes finishing together.
+struct ShadowQueue {
+    float4* __restrict__ rec;          // hit position xyz (voxel units), w = pixel bits (x | y << 15 | crosshair << 30)
+    uint32_t* __restrict__ aux;        // primary steps | normal code << 16
+    unsigned long long* __restrict__ count;
+};
+
+__device__ __forceinline__ void add_stats(unsigned long long* __restrict__ stats, uint32_t rays, uint32_t hits, uint32_t srays,
+                                          uint32_t shits, uint32_t steps, Work wk) {
+    const uint32_t m = __activemask();
+    const uint32_t leader = (uint32_t)__ffs((int)m) - 1u, lane = threadIdx.x & 31u;
+    const uint32_t v[8] = {rays, hits, srays, shits, steps, wk.C, wk.K, wk.E};
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const uint32_t sum = __reduce_add_sync(m, v[k]);
+        if (lane == leader && sum) atomicAdd(stats + k, (unsigned long long)sum);
+    }
+}
+
+// Everything screenDispatch does once the rays of a pixel are known (Renderer.cu:203-275).
+template <int NORM>
+__device__ __forceinline__ void emit_pixel(const FrameParams& f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane, uint32_t pix,
+                                           bool hit, V3 pos, uint32_t ncode, bool shadowed, int steps, V3 miss_dir) {
+    const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
+    const int W = (int)f.W, H = (int)f.H;
+    if (hit) {
+        const V3 nn = normal_from_code(ncode);
+        const V3 n = mk(-nn.x, -nn.y, -nn.z);
+        if (f.debug_view) { // Renderer.cu:215-243
+            const V3 dl = mk(fsub(pos.x, f.origin.x), fsub(pos.y, f.origin.y), fsub(pos.z, f.origin.z));
+            const float dist = __fsqrt_rn(dot3(dl, dl));
+            const float md = (float)(1.0 + kEpsDDA);
+            const V3 hp = mk(fmodf(fdiv(pos.x, 128.0f), md), fmodf(fdiv(pos.y, 128.0f), md), fmodf(fdiv(pos.z, 128.0f), md));
+            if (x < (W >> 1) && y < (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, n);
+            else if (x >= (W >> 1) && y < (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, hp);
+            else if (x < (W >> 1)) {}
+            else put_pixel(bgra, f.W, f.H, x, y, mk(fmul(dist, 0.01f), 0.0f, 0.0f));
+        } else {
+            put_pixel(bgra, f.W, f.H, x, y, shade<NORM>(f, n, pos, shadowed));
+        }
+    } else {
+        put_pixel(bgra, f.W, f.H, x, y, miss_dir); // miss: colour = ray direction, Renderer.cu:254-258
+    }
+    if (pix & (1u << 30)) put_pixel(bgra, f.W, f.H, x, y, mk(10.0f, 10.0f, 10.0f)); // crosshair, :260-268
+    if (f.debug_view && x < (W >> 1) && y > (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(fdiv((float)steps, 256.0f), 0.0f, 0.0f));
+    if (steps_plane) steps_plane[(size_t)y * f.W + x] = steps;
+}
+
 template <int NORM, bool STATS>
-struct RenderPolicy {
+struct PrimaryPolicy {
+    static constexpr int kRefill = 32; // a warp takes a whole tile at a time: neighbouring rays stay in step
     const FrameParams& f;
     uint8_t* __restrict__ bgra;
     int32_t* __restrict__ steps_plane;
     unsigned long long* __restrict__ stats;
-    // per lane
-    uint32_t pix;   // x | y << 15 | crosshair thread << 30
-    V3 ppos;        // primary hit (while the shadow ray marches)
-    uint32_t pn;    // primary normal code
-    int psteps;
-    Work pwork;
+    ShadowQueue q;
+    uint32_t pix; // per lane: x | y << 15 | crosshair thread << 30
 
-    __device__ __forceinline__ RenderPolicy(const FrameParams& fp, uint8_t* b, int32_t* sp, unsigned long long* st)
-        : f(fp), bgra(b), steps_plane(sp), stats(st), pix(0), pn(0), psteps(0) { ppos = mk(0.0f, 0.0f, 0.0f); pwork.C = pwork.K = pwork.E = 0; }
+    __device__ __forceinline__ PrimaryPolicy(const FrameParams& fp, uint8_t* b, int32_t* sp, unsigned long long* st, ShadowQueue sq)
+        : f(fp), bgra(b), steps_plane(sp), stats(st), q(sq), pix(0) {}
     __device__ __forceinline__ unsigned long long count() const { return f.ids; }
     __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
 
@@ -168,68 +220,79 @@ struct RenderPolicy {
 
     __device__ __forceinline__ void finish(const WorldView& w, Lane& L, V3 pos, uint32_t ncode) {
         const bool hit = L.flags & F_HIT;
-        bool phit, cast = false, shadowed = false;
-        int steps;
-        Work wk = L.work;
-        if (!(L.flags & F_SHADOW)) {
-            phit = hit;
-            steps = L.total;
-            if (hit && !f.debug_view && f.shadows) { // the shadow Raytrace of Renderer.cu:102: this lane becomes the shadow ray
-                ppos = pos; pn = ncode; psteps = L.total;
-                if (STATS) pwork = L.work;
-                const V3 sray = normalize3<NORM>(f.light);
-                const float ff = (float)w.factor;
-                const V3 so = mk(fadd(pos.x, fmul(sray.x, 0.01f)), fadd(pos.y, fmul(sray.y, 0.01f)), fadd(pos.z, fmul(sray.z, 0.01f)));
-                lane_setup(w, L, mk(fdiv(so.x, ff), fdiv(so.y, ff), fdiv(so.z, ff)), normalize3<NORM>(sray), F_SHADOW);
-                return;
-            }
-        } else {
-            phit = true; cast = true; shadowed = hit;
-            steps = psteps + L.total;
-            pos = ppos; ncode = pn;
-            if (STATS) { wk.C += pwork.C; wk.K += pwork.K; wk.E += pwork.E; }
-        }
-        const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
-        const int W = (int)f.W, H = (int)f.H;
-        if (phit) {
-            const V3 nn = normal_from_code(ncode);
-            const V3 n = mk(-nn.x, -nn.y, -nn.z);
-            if (f.debug_view) { // Renderer.cu:215-243
-                const V3 dl = mk(fsub(pos.x, f.origin.x), fsub(pos.y, f.origin.y), fsub(pos.z, f.origin.z));
-                const float dist = __fsqrt_rn(dot3(dl, dl));
-                const float md = (float)(1.0 + kEpsDDA);
-                const V3 hp = mk(fmodf(fdiv(pos.x, 128.0f), md), fmodf(fdiv(pos.y, 128.0f), md), fmodf(fdiv(pos.z, 128.0f), md));
-                if (x < (W >> 1) && y < (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, n);
-                else if (x >= (W >> 1) && y < (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, hp);
-                else if (x < (W >> 1)) {}
-                else put_pixel(bgra, f.W, f.H, x, y, mk(fmul(dist, 0.01f), 0.0f, 0.0f));
-            } else {
-                put_pixel(bgra, f.W, f.H, x, y, shade<NORM>(f, n, pos, shadowed));
-            }
-        } else {
-            put_pixel(bgra, f.W, f.H, x, y, primary_dir(x, y)); // miss: colour = ray direction, Renderer.cu:254-258
-        }
-        if (pix & (1u << 30)) put_pixel(bgra, f.W, f.H, x, y, mk(10.0f, 10.0f, 10.0f)); // crosshair, :260-268
-        if (f.debug_view && x < (W >> 1) && y > (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(fdiv((float)steps, 256.0f), 0.0f, 0.0f));
-        if (steps_plane) steps_plane[(size_t)y * f.W + x] = steps;
-        if (STATS) {
+        const bool queued = hit && !f.debug_view && f.shadows; // the shadow Raytrace of Renderer.cu:102 runs in shadow_rays
+        if (STATS) add_stats(stats, 1u, hit, 0u, 0u, queued ? 0u : (uint32_t)L.total, queued ? Work{0u, 0u, 0u} : L.work);
+        if (queued) {
             const uint32_t m = __activemask();
-            const uint32_t leader = (uint32_t)__ffs((int)m) - 1u, lane = threadIdx.x & 31u;
-            const uint32_t v[8] = {1u, (uint32_t)phit, (uint32_t)cast, (uint32_t)shadowed, (uint32_t)steps, wk.C, wk.K, wk.E};
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const uint32_t sum = __reduce_add_sync(m, v[k]);
-                if (lane == leader && sum) atomicAdd(stats + k, (unsigned long long)sum);
+            const uint32_t lane = threadIdx.x & 31u, leader = (uint32_t)__ffs((int)m) - 1u;
+            unsigned long long base = 0;
+            if (lane == leader) base = atomicAdd(q.count, (unsigned long long)__popc(m));
+            base = __shfl_sync(m, base, (int)leader);
+            const unsigned long long slot = base + (unsigned long long)__popc(m & ((1u << lane) - 1u));
+            q.rec[slot] = make_float4(pos.x, pos.y, pos.z, __uint_as_float(pix));
+            q.aux[slot] = (uint32_t)L.total | (ncode << 16);
+            if (STATS) { // the primary's steps and work are added when its pixel is finished
+                q.aux[slot + f.ids] = L.work.C; q.aux[slot + 2 * f.ids] = L.work.K; q.aux[slot + 3 * f.ids] = L.work.E;
             }
+        } else {
+            const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
+            emit_pixel<NORM>(f, bgra, steps_plane, pix, hit, pos, ncode, false, L.total, hit ? pos : primary_dir(x, y));
         }
         L.flags = ST_IDLE;
     }
 };
 
 template <int NORM, bool STATS>
-__global__ void __launch_bounds__(128) render_frame(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
-                                                    unsigned long long* __restrict__ stats, unsigned long long* next) {
-    RenderPolicy<NORM, STATS> pol(f, bgra, steps_plane, stats);
+struct ShadowPolicy {
+    static constexpr int kRefill = VX_REFILL_MIN;
+    const FrameParams& f;
+    uint8_t* __restrict__ bgra;
+    int32_t* __restrict__ steps_plane;
+    unsigned long long* __restrict__ stats;
+    ShadowQueue q;
+    unsigned long long n;
+    uint32_t slot; // per lane: queue entry whose shadow ray this lane marches
+
+    __device__ __forceinline__ ShadowPolicy(const FrameParams& fp, uint8_t* b, int32_t* sp, unsigned long long* st, ShadowQueue sq)
+        : f(fp), bgra(b), steps_plane(sp), stats(st), q(sq), n(*sq.count), slot(0) {}
+    __device__ __forceinline__ unsigned long long count() const { return n; }
+    __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
+
+    __device__ __forceinline__ void init(const WorldView& w, unsigned long long id, Lane& L) {
+        slot = (uint32_t)id;
+        const float4 r = q.rec[id];
+        // calculateColor, Renderer.cu:98-102: origin = position + normalize(L) * 0.01; Raytrace normalises again
+        const V3 sray = normalize3<NORM>(f.light);
+        const float ff = (float)w.factor;
+        const V3 so = mk(fadd(r.x, fmul(sray.x, 0.01f)), fadd(r.y, fmul(sray.y, 0.01f)), fadd(r.z, fmul(sray.z, 0.01f)));
+        lane_setup(w, L, mk(fdiv(so.x, ff), fdiv(so.y, ff), fdiv(so.z, ff)), normalize3<NORM>(sray), F_SHADOW);
+    }
+
+    __device__ __forceinline__ void finish(const WorldView& w, Lane& L, V3, uint32_t) {
+        const bool shadowed = L.flags & F_HIT;
+        const float4 r = q.rec[slot];
+        const uint32_t a = q.aux[slot];
+        const int steps = (int)(a & 0xFFFFu) + L.total;
+        if (STATS) {
+            Work wk = L.work;
+            wk.C += q.aux[slot + f.ids]; wk.K += q.aux[slot + 2 * f.ids]; wk.E += q.aux[slot + 3 * f.ids];
+            add_stats(stats, 0u, 0u, 1u, shadowed, (uint32_t)steps, wk);
+        }
+        emit_pixel<NORM>(f, bgra, steps_plane, __float_as_uint(r.w), true, mk(r.x, r.y, r.z), a >> 16, shadowed, steps, mk(0.0f, 0.0f, 0.0f));
+        L.flags = ST_IDLE;
+    }
+};
+
+template <int NORM, bool STATS>
+__global__ void __launch_bounds__(128) primary_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
+                                                    unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
+    PrimaryPolicy<NORM, STATS> pol(f, bgra, steps_plane, stats, q);
+    run_lanes<false, STATS>(w, pol, next);
+}
+template <int NORM, bool STATS>
+__global__ void __launch_bounds__(128) shadow_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
+                                                   unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
+    ShadowPolicy<NORM, STATS> pol(f, bgra, steps_plane, stats, q);
     run_lanes<false, STATS>(w, pol, next);
 }
 
@@ -274,7 +337,7 @@ extern "C" int vx_tracer_destroy(vx_tracer* t) {
     DeviceGuard guard(t->device);
     cudaFree(t->d_origins); cudaFree(t->d_dirs); cudaFree(t->d_hit); cudaFree(t->d_pos); cudaFree(t->d_normal);
     cudaFree(t->d_steps); cudaFree(t->d_voxel); cudaFree(t->d_brick); cudaFree(t->d_csteps); cudaFree(t->d_fsteps);
-    cudaFree(t->d_counters); cudaFree(t->d_frame); cudaFree(t->d_next);
+    cudaFree(t->d_counters); cudaFree(t->d_frame); cudaFree(t->d_next); cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux);
     if (t->stream) cudaStreamDestroy(t->stream);
     delete t;
     return VX_OK;
@@ -463,12 +526,32 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     const WorldView w = t->world->view();
     unsigned long long* st = (unsigned long long*)opts->d_stats;
     cudaStream_t cs = (cudaStream_t)stream;
-    unsigned long long* next = nullptr;
-    rc = next_counter(t, cs, &next);
+    const bool shadow_pass = opts->shadows && !opts->debug_view;
+    ShadowQueue q{nullptr, nullptr, nullptr};
+    if (shadow_pass) { // per-frame queue of primary hits waiting for their sun ray (one entry per pixel of this launch at most)
+        const size_t aux_words = (size_t)f.ids * (st ? 4u : 1u);
+        if (t->queue_cap < f.ids || t->queue_aux_words < aux_words) {
+            VX_CUDA(cudaStreamSynchronize(cs)); // frames in flight on this stream may still read the old queue
+            cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux); t->d_queue_rec = nullptr; t->d_queue_aux = nullptr; t->queue_cap = 0;
+            VX_CUDA(cudaMalloc(&t->d_queue_rec, (size_t)f.ids * sizeof(float4)));
+            VX_CUDA(cudaMalloc(&t->d_queue_aux, aux_words * sizeof(uint32_t)));
+            t->queue_cap = f.ids; t->queue_aux_words = aux_words;
+        }
+        q.rec = (float4*)t->d_queue_rec; q.aux = (uint32_t*)t->d_queue_aux;
+        unsigned long long* qc = nullptr;
+        rc = next_counter(t, cs, &qc);
+        if (rc) return rc;
+        q.count = qc;
+    }
+    unsigned long long *next1 = nullptr, *next2 = nullptr;
+    rc = next_counter(t, cs, &next1);
     if (rc) return rc;
+    if (shadow_pass) { rc = next_counter(t, cs, &next2); if (rc) return rc; }
     unsigned blocks = 1;
-#define VX_LAUNCH(N, S) do { rc = persistent_blocks(t, render_frame<N, S>, f.ids, blocks); if (rc) return rc; \
-        render_frame<N, S><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, next); } while (0)
+#define VX_LAUNCH(N, S) do { rc = persistent_blocks(t, primary_rays<N, S>, f.ids, blocks); if (rc) return rc; \
+        primary_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); \
+        if (shadow_pass) { rc = persistent_blocks(t, shadow_rays<N, S>, f.ids, blocks); if (rc) return rc; \
+            shadow_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next2); } } while (0)
     if (opts->norm_mode == VX_NORM_HOST) { if (st) VX_LAUNCH(1, true); else VX_LAUNCH(1, false); }
     else { if (st) VX_LAUNCH(0, true); else VX_LAUNCH(0, false); }
 #undef VX_LAUNCH
