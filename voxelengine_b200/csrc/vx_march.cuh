@@ -326,6 +326,8 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 //   void init(w, id, L)                   set the lane up for ray `id` (lane_setup) or leave it ST_IDLE
 //   void finish(w, L, pos, ncode)         consume a finished march and set the lane ST_IDLE (or re-arm it)
 //   kRefill                               idle lanes that trigger a refill (32: whole tiles only)
+//   kHandoff, void handoff(w, L)          optional: take a lane that spent a whole fast-loop chunk in empty cells out of
+//                                         this warp (the policy stores its state and sets ST_IDLE)
 // `next` is a zero-initialised device counter shared by all warps of the launch.
 // ---------------------------------------------------------------------------------------------
 #ifndef VX_REFILL_MIN
@@ -334,6 +336,11 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 #ifndef VX_FAST_CHUNK
 #define VX_FAST_CHUNK 64
 #endif
+#ifndef VX_LEAVE_NUM
+#define VX_LEAVE_NUM 1
+#define VX_LEAVE_DEN 4
+#endif
+constexpr int kFastQuad = 4;                // fast-loop steps between looks at how many lanes are still stepping
 constexpr int kChunk = 32;                  // ray ids a warp draws at a time (render: one 8x4 pixel tile)
 constexpr int kFastChunk = VX_FAST_CHUNK;   // coarse steps a lane may take before the warp looks at the other states again
 
@@ -360,13 +367,28 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
             float tx = L.tx, ty = L.ty, tz = L.tz;
             uint32_t idx = L.idx;
             int budget = kFastChunk;
-#pragma unroll 4
+            // Lanes leave this loop one by one as they meet occupied cells.  Once most of the lanes that entered it are
+            // waiting, the few still stepping stop too (they stay ST_FAST and go on in the next round): a warp serves
+            // its majority.  Checked every kFastQuad steps; a scheduling heuristic only, results do not depend on it.
+            const int entered = __popc(__activemask());
+            bool found = false;
+#pragma unroll 1
             do {
-                if (cell_bit(w.ptop, idx)) { lane_set_state(L, ST_CAND); break; }
-                if (COUNT) L.work.C++;
-                fast_step(tx, ty, tz, idx, dtx, dty, dtz, dix, diy, diz);
-            } while (--budget);
+#pragma unroll
+                for (int k = 0; k < kFastQuad; ++k) {
+                    if (cell_bit(w.ptop, idx)) { found = true; break; }
+                    if (COUNT) L.work.C++;
+                    fast_step(tx, ty, tz, idx, dtx, dty, dtz, dix, diy, diz);
+                }
+                if (found) { lane_set_state(L, ST_CAND); break; }
+                budget -= kFastQuad;
+#ifdef VX_NOVOTE
+            } while (budget > 0);
+#else
+            } while (budget > 0 && __popc(__activemask()) * VX_LEAVE_DEN >= entered * VX_LEAVE_NUM);
+#endif
             L.tx = tx; L.ty = ty; L.tz = tz; L.idx = idx; L.bidx = idx;
+            if (Policy::kHandoff && budget <= 0 && !found) pol.handoff(w, L); // a whole chunk of empty cells: let the policy park the ray
         }
         if (lane_state(L) == ST_SLOW) lane_slow<COUNT>(w, L);
         if (lane_state(L) == ST_CAND) lane_cand<BATCH, COUNT>(w, L, pos, ncode);

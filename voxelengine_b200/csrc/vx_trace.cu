@@ -7,6 +7,10 @@
 #include "vx_host.h"
 #include "vx_march.cuh"
 
+#ifndef VX_MIN_BLOCKS
+#define VX_MIN_BLOCKS 8 // resident 128-thread blocks per SM the render kernels are compiled for (register budget)
+#endif
+
 namespace vx {
 
 struct HitPlanes {
@@ -24,6 +28,8 @@ struct BatchPolicy {
     HitPlanes out;
     unsigned long long id; // per lane: the ray being marched
     static constexpr int kRefill = VX_REFILL_MIN;
+    static constexpr bool kHandoff = false;
+    __device__ __forceinline__ void handoff(const WorldView&, Lane&) {}
 
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return cap; }
@@ -130,6 +136,10 @@ struct ShadowQueue {
     float4* __restrict__ rec;          // hit position xyz (voxel units), w = pixel bits (x | y << 15 | crosshair << 30)
     uint32_t* __restrict__ aux;        // primary steps | normal code << 16
     unsigned long long* __restrict__ count;
+    // cruise queue: sun rays that ran a whole fast-loop chunk through empty cells are parked here with their march state
+    // and finished by shadow_rays<.., CRUISE>, whose warps then hold nothing but such rays
+    uint4* __restrict__ cruise;        // 3 x uint4 per entry (+1 with STATS): s.xyz tx | ty tz idx total | pc flags slot 0 | C K E 0
+    unsigned long long* __restrict__ cruise_count;
 };
 
 __device__ __forceinline__ void add_stats(unsigned long long* __restrict__ stats, uint32_t rays, uint32_t hits, uint32_t srays,
@@ -176,6 +186,8 @@ __device__ __forceinline__ void emit_pixel(const FrameParams& f, uint8_t* __rest
 template <int NORM, bool STATS>
 struct PrimaryPolicy {
     static constexpr int kRefill = 32; // a warp takes a whole tile at a time: neighbouring rays stay in step
+    static constexpr bool kHandoff = false;
+    __device__ __forceinline__ void handoff(const WorldView&, Lane&) {}
     const FrameParams& f;
     uint8_t* __restrict__ bgra;
     int32_t* __restrict__ steps_plane;
@@ -242,9 +254,11 @@ struct PrimaryPolicy {
     }
 };
 
-template <int NORM, bool STATS>
+template <int NORM, bool STATS, bool CRUISE>
 struct ShadowPolicy {
     static constexpr int kRefill = VX_REFILL_MIN;
+    static constexpr bool kHandoff = !CRUISE;
+    static constexpr int kRecWords = STATS ? 4 : 3; // uint4 per cruise entry
     const FrameParams& f;
     uint8_t* __restrict__ bgra;
     int32_t* __restrict__ steps_plane;
@@ -254,18 +268,42 @@ struct ShadowPolicy {
     uint32_t slot; // per lane: queue entry whose shadow ray this lane marches
 
     __device__ __forceinline__ ShadowPolicy(const FrameParams& fp, uint8_t* b, int32_t* sp, unsigned long long* st, ShadowQueue sq)
-        : f(fp), bgra(b), steps_plane(sp), stats(st), q(sq), n(*sq.count), slot(0) {}
+        : f(fp), bgra(b), steps_plane(sp), stats(st), q(sq), n(CRUISE ? *sq.cruise_count : *sq.count), slot(0) {}
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
 
     __device__ __forceinline__ void init(const WorldView& w, unsigned long long id, Lane& L) {
-        slot = (uint32_t)id;
-        const float4 r = q.rec[id];
         // calculateColor, Renderer.cu:98-102: origin = position + normalize(L) * 0.01; Raytrace normalises again
         const V3 sray = normalize3<NORM>(f.light);
+        if (CRUISE) { // resume a parked ray: everything but the direction-derived values comes from its record
+            const uint4 a = q.cruise[id * kRecWords], b = q.cruise[id * kRecWords + 1], c = q.cruise[id * kRecWords + 2];
+            lane_setup(w, L, mk(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z)), normalize3<NORM>(sray), 0u);
+            L.s = mk(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z)); // (lane_setup may clip a start outside the grid)
+            L.tx = __uint_as_float(a.w); L.ty = __uint_as_float(b.x); L.tz = __uint_as_float(b.y);
+            L.idx = b.z; L.total = (int)b.w; L.pc = c.x; L.flags = c.y; slot = c.z;
+            if (STATS) { const uint4 d = q.cruise[id * kRecWords + 3]; L.work.C = d.x; L.work.K = d.y; L.work.E = d.z; }
+            return;
+        }
+        slot = (uint32_t)id;
+        const float4 r = q.rec[id];
         const float ff = (float)w.factor;
         const V3 so = mk(fadd(r.x, fmul(sray.x, 0.01f)), fadd(r.y, fmul(sray.y, 0.01f)), fadd(r.z, fmul(sray.z, 0.01f)));
         lane_setup(w, L, mk(fdiv(so.x, ff), fdiv(so.y, ff), fdiv(so.z, ff)), normalize3<NORM>(sray), F_SHADOW);
+    }
+
+    // A lane that used up a fast-loop chunk without meeting an occupied cell: park it (warp-aggregated append).
+    __device__ __forceinline__ void handoff(const WorldView&, Lane& L) {
+        const uint32_t m = __activemask();
+        const uint32_t lane = threadIdx.x & 31u, leader = (uint32_t)__ffs((int)m) - 1u;
+        unsigned long long base = 0;
+        if (lane == leader) base = atomicAdd(q.cruise_count, (unsigned long long)__popc(m));
+        base = __shfl_sync(m, base, (int)leader);
+        const unsigned long long e = (base + (unsigned long long)__popc(m & ((1u << lane) - 1u))) * kRecWords;
+        q.cruise[e] = make_uint4(__float_as_uint(L.s.x), __float_as_uint(L.s.y), __float_as_uint(L.s.z), __float_as_uint(L.tx));
+        q.cruise[e + 1] = make_uint4(__float_as_uint(L.ty), __float_as_uint(L.tz), L.idx, (uint32_t)L.total);
+        q.cruise[e + 2] = make_uint4(L.pc, L.flags, slot, 0u);
+        if (STATS) q.cruise[e + 3] = make_uint4(L.work.C, L.work.K, L.work.E, 0u);
+        L.flags = ST_IDLE;
     }
 
     __device__ __forceinline__ void finish(const WorldView& w, Lane& L, V3, uint32_t) {
@@ -284,15 +322,15 @@ struct ShadowPolicy {
 };
 
 template <int NORM, bool STATS>
-__global__ void __launch_bounds__(128) primary_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
+__global__ void __launch_bounds__(128, VX_MIN_BLOCKS) primary_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
                                                     unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
     PrimaryPolicy<NORM, STATS> pol(f, bgra, steps_plane, stats, q);
     run_lanes<false, STATS>(w, pol, next);
 }
-template <int NORM, bool STATS>
-__global__ void __launch_bounds__(128) shadow_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
+template <int NORM, bool STATS, bool CRUISE>
+__global__ void __launch_bounds__(128, VX_MIN_BLOCKS) shadow_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
                                                    unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
-    ShadowPolicy<NORM, STATS> pol(f, bgra, steps_plane, stats, q);
+    ShadowPolicy<NORM, STATS, CRUISE> pol(f, bgra, steps_plane, stats, q);
     run_lanes<false, STATS>(w, pol, next);
 }
 
@@ -337,7 +375,7 @@ extern "C" int vx_tracer_destroy(vx_tracer* t) {
     DeviceGuard guard(t->device);
     cudaFree(t->d_origins); cudaFree(t->d_dirs); cudaFree(t->d_hit); cudaFree(t->d_pos); cudaFree(t->d_normal);
     cudaFree(t->d_steps); cudaFree(t->d_voxel); cudaFree(t->d_brick); cudaFree(t->d_csteps); cudaFree(t->d_fsteps);
-    cudaFree(t->d_counters); cudaFree(t->d_frame); cudaFree(t->d_next); cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux);
+    cudaFree(t->d_counters); cudaFree(t->d_frame); cudaFree(t->d_next); cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux); cudaFree(t->d_queue_cruise);
     if (t->stream) cudaStreamDestroy(t->stream);
     delete t;
     return VX_OK;
@@ -527,7 +565,7 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     unsigned long long* st = (unsigned long long*)opts->d_stats;
     cudaStream_t cs = (cudaStream_t)stream;
     const bool shadow_pass = opts->shadows && !opts->debug_view;
-    ShadowQueue q{nullptr, nullptr, nullptr};
+    ShadowQueue q{nullptr, nullptr, nullptr, nullptr, nullptr};
     if (shadow_pass) { // per-frame queue of primary hits waiting for their sun ray (one entry per pixel of this launch at most)
         const size_t aux_words = (size_t)f.ids * (st ? 4u : 1u);
         if (t->queue_cap < f.ids || t->queue_aux_words < aux_words) {
@@ -535,23 +573,31 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
             cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux); t->d_queue_rec = nullptr; t->d_queue_aux = nullptr; t->queue_cap = 0;
             VX_CUDA(cudaMalloc(&t->d_queue_rec, (size_t)f.ids * sizeof(float4)));
             VX_CUDA(cudaMalloc(&t->d_queue_aux, aux_words * sizeof(uint32_t)));
+            cudaFree(t->d_queue_cruise); t->d_queue_cruise = nullptr;
+            VX_CUDA(cudaMalloc(&t->d_queue_cruise, (size_t)f.ids * 4u * sizeof(uint4)));
             t->queue_cap = f.ids; t->queue_aux_words = aux_words;
         }
-        q.rec = (float4*)t->d_queue_rec; q.aux = (uint32_t*)t->d_queue_aux;
+        q.rec = (float4*)t->d_queue_rec; q.aux = (uint32_t*)t->d_queue_aux; q.cruise = (uint4*)t->d_queue_cruise;
+        unsigned long long* cc = nullptr;
+        rc = next_counter(t, cs, &cc);
+        if (rc) return rc;
+        q.cruise_count = cc;
         unsigned long long* qc = nullptr;
         rc = next_counter(t, cs, &qc);
         if (rc) return rc;
         q.count = qc;
     }
-    unsigned long long *next1 = nullptr, *next2 = nullptr;
+    unsigned long long *next1 = nullptr, *next2 = nullptr, *next3 = nullptr;
     rc = next_counter(t, cs, &next1);
     if (rc) return rc;
-    if (shadow_pass) { rc = next_counter(t, cs, &next2); if (rc) return rc; }
+    if (shadow_pass) { rc = next_counter(t, cs, &next2); if (rc) return rc; rc = next_counter(t, cs, &next3); if (rc) return rc; }
     unsigned blocks = 1;
 #define VX_LAUNCH(N, S) do { rc = persistent_blocks(t, primary_rays<N, S>, f.ids, blocks); if (rc) return rc; \
         primary_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); \
-        if (shadow_pass) { rc = persistent_blocks(t, shadow_rays<N, S>, f.ids, blocks); if (rc) return rc; \
-            shadow_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next2); } } while (0)
+        if (shadow_pass) { rc = persistent_blocks(t, shadow_rays<N, S, false>, f.ids, blocks); if (rc) return rc; \
+            shadow_rays<N, S, false><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next2); \
+            rc = persistent_blocks(t, shadow_rays<N, S, true>, f.ids, blocks); if (rc) return rc; \
+            shadow_rays<N, S, true><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next3); } } while (0)
     if (opts->norm_mode == VX_NORM_HOST) { if (st) VX_LAUNCH(1, true); else VX_LAUNCH(1, false); }
     else { if (st) VX_LAUNCH(0, true); else VX_LAUNCH(0, false); }
 #undef VX_LAUNCH
