@@ -95,7 +95,7 @@ struct vx_tracer {
     cudaStream_t stream = nullptr;
     unsigned long long* d_next = nullptr;            // ring of ray counters for the persistent kernels
     unsigned next_seq = 0;
-    void* d_queue_rec = nullptr; void* d_queue_aux = nullptr; void* d_queue_cruise = nullptr;   // shadow queue of vx_render (one frame in flight per tracer)
+    void* d_queue_rec = nullptr; void* d_queue_aux = nullptr; void* d_queue_lanes = nullptr;   // shadow queue of vx_render (one frame in flight per tracer)
     unsigned long long queue_cap = 0; size_t queue_aux_words = 0;
     int sm_count = 0;
 };

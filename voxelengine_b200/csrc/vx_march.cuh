@@ -326,8 +326,6 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 //   void init(w, id, L)                   set the lane up for ray `id` (lane_setup) or leave it ST_IDLE
 //   void finish(w, L, pos, ncode)         consume a finished march and set the lane ST_IDLE (or re-arm it)
 //   kRefill                               idle lanes that trigger a refill (32: whole tiles only)
-//   kHandoff, void handoff(w, L)          optional: take a lane that spent a whole fast-loop chunk in empty cells out of
-//                                         this warp (the policy stores its state and sets ST_IDLE)
 // `next` is a zero-initialised device counter shared by all warps of the launch.
 // ---------------------------------------------------------------------------------------------
 #ifndef VX_REFILL_MIN
@@ -388,7 +386,6 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
             } while (budget > 0 && __popc(__activemask()) * VX_LEAVE_DEN >= entered * VX_LEAVE_NUM);
 #endif
             L.tx = tx; L.ty = ty; L.tz = tz; L.idx = idx; L.bidx = idx;
-            if (Policy::kHandoff && budget <= 0 && !found) pol.handoff(w, L); // a whole chunk of empty cells: let the policy park the ray
         }
         if (lane_state(L) == ST_SLOW) lane_slow<COUNT>(w, L);
         if (lane_state(L) == ST_CAND) lane_cand<BATCH, COUNT>(w, L, pos, ncode);

@@ -28,8 +28,6 @@ struct BatchPolicy {
     HitPlanes out;
     unsigned long long id; // per lane: the ray being marched
     static constexpr int kRefill = VX_REFILL_MIN;
-    static constexpr bool kHandoff = false;
-    __device__ __forceinline__ void handoff(const WorldView&, Lane&) {}
 
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return cap; }
@@ -133,13 +131,12 @@ __device__ __forceinline__ V3 shade(const FrameParams& f, V3 n, V3 pos, bool sha
 // STATS: per-frame counters (8 x uint64: primary rays, primary hits, shadow rays, shadow hits, steps, C, K, E —
 // SURVEY.md §8d), added with one atomic per group of lanes finishing together.
 struct ShadowQueue {
-    float4* __restrict__ rec;          // hit position xyz (voxel units), w = pixel bits (x | y << 15 | crosshair << 30)
-    uint32_t* __restrict__ aux;        // primary steps | normal code << 16
+    float4* __restrict__ rec;          // primary hit: position xyz (voxel units), w = pixel bits (x | y << 15 | crosshair << 30)
+    uint32_t* __restrict__ aux;        // planes of `ids` words: 0 primary steps | normal code << 16, 1 sun-ray steps | hit << 31,
+                                       // with STATS also 2-4 primary C,K,E and 5-7 sun-ray C,K,E
+    uint4* __restrict__ lanes;         // 3 x uint4 per entry: the sun ray's march state after set-up and its first
+                                       // traversal start (s.xyz tx | ty tz idx total | pc flags 0 0), written by shadow_setup
     unsigned long long* __restrict__ count;
-    // cruise queue: sun rays that ran a whole fast-loop chunk through empty cells are parked here with their march state
-    // and finished by shadow_rays<.., CRUISE>, whose warps then hold nothing but such rays
-    uint4* __restrict__ cruise;        // 3 x uint4 per entry (+1 with STATS): s.xyz tx | ty tz idx total | pc flags slot 0 | C K E 0
-    unsigned long long* __restrict__ cruise_count;
 };
 
 __device__ __forceinline__ void add_stats(unsigned long long* __restrict__ stats, uint32_t rays, uint32_t hits, uint32_t srays,
@@ -186,8 +183,6 @@ __device__ __forceinline__ void emit_pixel(const FrameParams& f, uint8_t* __rest
 template <int NORM, bool STATS>
 struct PrimaryPolicy {
     static constexpr int kRefill = 32; // a warp takes a whole tile at a time: neighbouring rays stay in step
-    static constexpr bool kHandoff = false;
-    __device__ __forceinline__ void handoff(const WorldView&, Lane&) {}
     const FrameParams& f;
     uint8_t* __restrict__ bgra;
     int32_t* __restrict__ steps_plane;
@@ -244,7 +239,7 @@ struct PrimaryPolicy {
             q.rec[slot] = make_float4(pos.x, pos.y, pos.z, __uint_as_float(pix));
             q.aux[slot] = (uint32_t)L.total | (ncode << 16);
             if (STATS) { // the primary's steps and work are added when its pixel is finished
-                q.aux[slot + f.ids] = L.work.C; q.aux[slot + 2 * f.ids] = L.work.K; q.aux[slot + 3 * f.ids] = L.work.E;
+                q.aux[slot + 2 * f.ids] = L.work.C; q.aux[slot + 3 * f.ids] = L.work.K; q.aux[slot + 4 * f.ids] = L.work.E;
             }
         } else {
             const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
@@ -254,83 +249,100 @@ struct PrimaryPolicy {
     }
 };
 
-template <int NORM, bool STATS, bool CRUISE>
+// Sun rays.  Set-up (origin, grid-entry clip, first traversal start: six IEEE divisions per ray) and shading (powf,
+// tonemap) are the same straight-line work for every ray, so they run as dense one-thread-per-entry kernels around
+// the march instead of inside it, where lanes finish and start one by one:
+//   shadow_setup  queue entry -> lane record          (dense)
+//   shadow_rays   lane record -> steps | hit          (persistent warps, the divergent part)
+//   shade_pixels  entry + result -> pixel             (dense)
+template <int NORM>
+__device__ __forceinline__ V3 sun_direction(const FrameParams& f, V3& once) {
+    // calculateColor, Renderer.cu:98-102: shadowRay = normalize(L); Raytrace normalises what it is given again (:363)
+    once = normalize3<NORM>(f.light);
+    return normalize3<NORM>(once);
+}
+
+template <int NORM>
+__global__ void __launch_bounds__(256) shadow_setup(WorldView w, FrameParams f, ShadowQueue q) {
+    const unsigned long long n = *q.count;
+    V3 sray;
+    const V3 d = sun_direction<NORM>(f, sray);
+    const float ff = (float)w.factor;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const float4 r = q.rec[i];
+        const V3 so = mk(fadd(r.x, fmul(sray.x, 0.01f)), fadd(r.y, fmul(sray.y, 0.01f)), fadd(r.z, fmul(sray.z, 0.01f)));
+        Lane L;
+        lane_setup(w, L, mk(fdiv(so.x, ff), fdiv(so.y, ff), fdiv(so.z, ff)), d, F_SHADOW);
+        L.tx = L.ty = L.tz = 0.0f; L.idx = 0;
+        lane_begin(w, L, kMaxSteps);
+        q.lanes[3 * i] = make_uint4(__float_as_uint(L.s.x), __float_as_uint(L.s.y), __float_as_uint(L.s.z), __float_as_uint(L.tx));
+        q.lanes[3 * i + 1] = make_uint4(__float_as_uint(L.ty), __float_as_uint(L.tz), L.idx, 0u);
+        q.lanes[3 * i + 2] = make_uint4(L.pc, L.flags, 0u, 0u);
+    }
+}
+
+template <int NORM, bool STATS>
 struct ShadowPolicy {
     static constexpr int kRefill = VX_REFILL_MIN;
-    static constexpr bool kHandoff = !CRUISE;
-    static constexpr int kRecWords = STATS ? 4 : 3; // uint4 per cruise entry
     const FrameParams& f;
-    uint8_t* __restrict__ bgra;
-    int32_t* __restrict__ steps_plane;
-    unsigned long long* __restrict__ stats;
     ShadowQueue q;
     unsigned long long n;
-    uint32_t slot; // per lane: queue entry whose shadow ray this lane marches
+    V3 d; float ivx, ivy, ivz; // the same for every sun ray
+    uint32_t slot;             // per lane: queue entry whose sun ray this lane marches
 
-    __device__ __forceinline__ ShadowPolicy(const FrameParams& fp, uint8_t* b, int32_t* sp, unsigned long long* st, ShadowQueue sq)
-        : f(fp), bgra(b), steps_plane(sp), stats(st), q(sq), n(CRUISE ? *sq.cruise_count : *sq.count), slot(0) {}
+    __device__ __forceinline__ ShadowPolicy(const FrameParams& fp, ShadowQueue sq) : f(fp), q(sq), n(*sq.count), slot(0) {
+        V3 once;
+        d = sun_direction<NORM>(f, once);
+        ivx = fdiv(1.0f, d.x == 0.0f ? kFltEps : d.x); ivy = fdiv(1.0f, d.y == 0.0f ? kFltEps : d.y); ivz = fdiv(1.0f, d.z == 0.0f ? kFltEps : d.z);
+    }
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
 
-    __device__ __forceinline__ void init(const WorldView& w, unsigned long long id, Lane& L) {
-        // calculateColor, Renderer.cu:98-102: origin = position + normalize(L) * 0.01; Raytrace normalises again
-        const V3 sray = normalize3<NORM>(f.light);
-        if (CRUISE) { // resume a parked ray: everything but the direction-derived values comes from its record
-            const uint4 a = q.cruise[id * kRecWords], b = q.cruise[id * kRecWords + 1], c = q.cruise[id * kRecWords + 2];
-            lane_setup(w, L, mk(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z)), normalize3<NORM>(sray), 0u);
-            L.s = mk(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z)); // (lane_setup may clip a start outside the grid)
-            L.tx = __uint_as_float(a.w); L.ty = __uint_as_float(b.x); L.tz = __uint_as_float(b.y);
-            L.idx = b.z; L.total = (int)b.w; L.pc = c.x; L.flags = c.y; slot = c.z;
-            if (STATS) { const uint4 d = q.cruise[id * kRecWords + 3]; L.work.C = d.x; L.work.K = d.y; L.work.E = d.z; }
-            return;
-        }
+    __device__ __forceinline__ void init(const WorldView&, unsigned long long id, Lane& L) {
         slot = (uint32_t)id;
-        const float4 r = q.rec[id];
-        const float ff = (float)w.factor;
-        const V3 so = mk(fadd(r.x, fmul(sray.x, 0.01f)), fadd(r.y, fmul(sray.y, 0.01f)), fadd(r.z, fmul(sray.z, 0.01f)));
-        lane_setup(w, L, mk(fdiv(so.x, ff), fdiv(so.y, ff), fdiv(so.z, ff)), normalize3<NORM>(sray), F_SHADOW);
+        const uint4 a = q.lanes[3 * id], b = q.lanes[3 * id + 1], c = q.lanes[3 * id + 2];
+        L.d = d; L.ivx = ivx; L.ivy = ivy; L.ivz = ivz;
+        L.s = mk(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z));
+        L.tx = __uint_as_float(a.w); L.ty = __uint_as_float(b.x); L.tz = __uint_as_float(b.y);
+        L.idx = b.z; L.total = 0; L.pc = c.x; L.flags = c.y;
+        L.csteps = 0; L.fsteps = 0; L.fcell = 0; L.work.C = L.work.K = L.work.E = 0;
     }
 
-    // A lane that used up a fast-loop chunk without meeting an occupied cell: park it (warp-aggregated append).
-    __device__ __forceinline__ void handoff(const WorldView&, Lane& L) {
-        const uint32_t m = __activemask();
-        const uint32_t lane = threadIdx.x & 31u, leader = (uint32_t)__ffs((int)m) - 1u;
-        unsigned long long base = 0;
-        if (lane == leader) base = atomicAdd(q.cruise_count, (unsigned long long)__popc(m));
-        base = __shfl_sync(m, base, (int)leader);
-        const unsigned long long e = (base + (unsigned long long)__popc(m & ((1u << lane) - 1u))) * kRecWords;
-        q.cruise[e] = make_uint4(__float_as_uint(L.s.x), __float_as_uint(L.s.y), __float_as_uint(L.s.z), __float_as_uint(L.tx));
-        q.cruise[e + 1] = make_uint4(__float_as_uint(L.ty), __float_as_uint(L.tz), L.idx, (uint32_t)L.total);
-        q.cruise[e + 2] = make_uint4(L.pc, L.flags, slot, 0u);
-        if (STATS) q.cruise[e + 3] = make_uint4(L.work.C, L.work.K, L.work.E, 0u);
-        L.flags = ST_IDLE;
-    }
-
-    __device__ __forceinline__ void finish(const WorldView& w, Lane& L, V3, uint32_t) {
-        const bool shadowed = L.flags & F_HIT;
-        const float4 r = q.rec[slot];
-        const uint32_t a = q.aux[slot];
-        const int steps = (int)(a & 0xFFFFu) + L.total;
-        if (STATS) {
-            Work wk = L.work;
-            wk.C += q.aux[slot + f.ids]; wk.K += q.aux[slot + 2 * f.ids]; wk.E += q.aux[slot + 3 * f.ids];
-            add_stats(stats, 0u, 0u, 1u, shadowed, (uint32_t)steps, wk);
-        }
-        emit_pixel<NORM>(f, bgra, steps_plane, __float_as_uint(r.w), true, mk(r.x, r.y, r.z), a >> 16, shadowed, steps, mk(0.0f, 0.0f, 0.0f));
+    __device__ __forceinline__ void finish(const WorldView&, Lane& L, V3, uint32_t) {
+        q.aux[slot + f.ids] = (uint32_t)L.total | ((L.flags & F_HIT) ? 0x80000000u : 0u);
+        if (STATS) { q.aux[slot + 5 * f.ids] = L.work.C; q.aux[slot + 6 * f.ids] = L.work.K; q.aux[slot + 7 * f.ids] = L.work.E; }
         L.flags = ST_IDLE;
     }
 };
 
 template <int NORM, bool STATS>
+__global__ void __launch_bounds__(256) shade_pixels(FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
+                                                    unsigned long long* __restrict__ stats, ShadowQueue q) {
+    const unsigned long long n = *q.count;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const float4 r = q.rec[i];
+        const uint32_t a = q.aux[i], b = q.aux[i + f.ids];
+        const bool shadowed = b >> 31;
+        const int steps = (int)(a & 0xFFFFu) + (int)(b & 0x7FFFFFFFu);
+        if (STATS) {
+            Work wk;
+            wk.C = q.aux[i + 2 * f.ids] + q.aux[i + 5 * f.ids]; wk.K = q.aux[i + 3 * f.ids] + q.aux[i + 6 * f.ids];
+            wk.E = q.aux[i + 4 * f.ids] + q.aux[i + 7 * f.ids];
+            add_stats(stats, 0u, 0u, 1u, shadowed, (uint32_t)steps, wk);
+        }
+        emit_pixel<NORM>(f, bgra, steps_plane, __float_as_uint(r.w), true, mk(r.x, r.y, r.z), a >> 16, shadowed, steps, mk(0.0f, 0.0f, 0.0f));
+    }
+}
+
+template <int NORM, bool STATS>
 __global__ void __launch_bounds__(128, VX_MIN_BLOCKS) primary_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
-                                                    unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
+                                                                   unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
     PrimaryPolicy<NORM, STATS> pol(f, bgra, steps_plane, stats, q);
     run_lanes<false, STATS>(w, pol, next);
 }
-template <int NORM, bool STATS, bool CRUISE>
-__global__ void __launch_bounds__(128, VX_MIN_BLOCKS) shadow_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
-                                                   unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
-    ShadowPolicy<NORM, STATS, CRUISE> pol(f, bgra, steps_plane, stats, q);
+template <int NORM, bool STATS>
+__global__ void __launch_bounds__(128, VX_MIN_BLOCKS) shadow_rays(WorldView w, FrameParams f, ShadowQueue q, unsigned long long* next) {
+    ShadowPolicy<NORM, STATS> pol(f, q);
     run_lanes<false, STATS>(w, pol, next);
 }
 
@@ -375,7 +387,7 @@ extern "C" int vx_tracer_destroy(vx_tracer* t) {
     DeviceGuard guard(t->device);
     cudaFree(t->d_origins); cudaFree(t->d_dirs); cudaFree(t->d_hit); cudaFree(t->d_pos); cudaFree(t->d_normal);
     cudaFree(t->d_steps); cudaFree(t->d_voxel); cudaFree(t->d_brick); cudaFree(t->d_csteps); cudaFree(t->d_fsteps);
-    cudaFree(t->d_counters); cudaFree(t->d_frame); cudaFree(t->d_next); cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux); cudaFree(t->d_queue_cruise);
+    cudaFree(t->d_counters); cudaFree(t->d_frame); cudaFree(t->d_next); cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux); cudaFree(t->d_queue_lanes);
     if (t->stream) cudaStreamDestroy(t->stream);
     delete t;
     return VX_OK;
@@ -565,39 +577,37 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     unsigned long long* st = (unsigned long long*)opts->d_stats;
     cudaStream_t cs = (cudaStream_t)stream;
     const bool shadow_pass = opts->shadows && !opts->debug_view;
-    ShadowQueue q{nullptr, nullptr, nullptr, nullptr, nullptr};
+    ShadowQueue q{nullptr, nullptr, nullptr, nullptr};
     if (shadow_pass) { // per-frame queue of primary hits waiting for their sun ray (one entry per pixel of this launch at most)
-        const size_t aux_words = (size_t)f.ids * (st ? 4u : 1u);
+        const size_t aux_words = (size_t)f.ids * (st ? 8u : 2u);
         if (t->queue_cap < f.ids || t->queue_aux_words < aux_words) {
             VX_CUDA(cudaStreamSynchronize(cs)); // frames in flight on this stream may still read the old queue
-            cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux); t->d_queue_rec = nullptr; t->d_queue_aux = nullptr; t->queue_cap = 0;
+            cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux); cudaFree(t->d_queue_lanes);
+            t->d_queue_rec = nullptr; t->d_queue_aux = nullptr; t->d_queue_lanes = nullptr; t->queue_cap = 0; t->queue_aux_words = 0;
             VX_CUDA(cudaMalloc(&t->d_queue_rec, (size_t)f.ids * sizeof(float4)));
             VX_CUDA(cudaMalloc(&t->d_queue_aux, aux_words * sizeof(uint32_t)));
-            cudaFree(t->d_queue_cruise); t->d_queue_cruise = nullptr;
-            VX_CUDA(cudaMalloc(&t->d_queue_cruise, (size_t)f.ids * 4u * sizeof(uint4)));
+            VX_CUDA(cudaMalloc(&t->d_queue_lanes, (size_t)f.ids * 3u * sizeof(uint4)));
             t->queue_cap = f.ids; t->queue_aux_words = aux_words;
         }
-        q.rec = (float4*)t->d_queue_rec; q.aux = (uint32_t*)t->d_queue_aux; q.cruise = (uint4*)t->d_queue_cruise;
-        unsigned long long* cc = nullptr;
-        rc = next_counter(t, cs, &cc);
-        if (rc) return rc;
-        q.cruise_count = cc;
+        q.rec = (float4*)t->d_queue_rec; q.aux = (uint32_t*)t->d_queue_aux; q.lanes = (uint4*)t->d_queue_lanes;
         unsigned long long* qc = nullptr;
         rc = next_counter(t, cs, &qc);
         if (rc) return rc;
         q.count = qc;
     }
-    unsigned long long *next1 = nullptr, *next2 = nullptr, *next3 = nullptr;
+    unsigned long long *next1 = nullptr, *next2 = nullptr;
     rc = next_counter(t, cs, &next1);
     if (rc) return rc;
-    if (shadow_pass) { rc = next_counter(t, cs, &next2); if (rc) return rc; rc = next_counter(t, cs, &next3); if (rc) return rc; }
+    if (shadow_pass) { rc = next_counter(t, cs, &next2); if (rc) return rc; }
     unsigned blocks = 1;
+    const unsigned dense_blocks = (unsigned)(t->sm_count > 0 ? t->sm_count : 148) * 8u; // grid-stride over a device-side count
 #define VX_LAUNCH(N, S) do { rc = persistent_blocks(t, primary_rays<N, S>, f.ids, blocks); if (rc) return rc; \
         primary_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); \
-        if (shadow_pass) { rc = persistent_blocks(t, shadow_rays<N, S, false>, f.ids, blocks); if (rc) return rc; \
-            shadow_rays<N, S, false><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next2); \
-            rc = persistent_blocks(t, shadow_rays<N, S, true>, f.ids, blocks); if (rc) return rc; \
-            shadow_rays<N, S, true><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next3); } } while (0)
+        if (shadow_pass) { \
+            shadow_setup<N><<<dense_blocks, 256, 0, cs>>>(w, f, q); \
+            rc = persistent_blocks(t, shadow_rays<N, S>, f.ids, blocks); if (rc) return rc; \
+            shadow_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, q, next2); \
+            shade_pixels<N, S><<<dense_blocks, 256, 0, cs>>>(f, (uint8_t*)d_bgra, d_steps, st, q); } } while (0)
     if (opts->norm_mode == VX_NORM_HOST) { if (st) VX_LAUNCH(1, true); else VX_LAUNCH(1, false); }
     else { if (st) VX_LAUNCH(0, true); else VX_LAUNCH(0, false); }
 #undef VX_LAUNCH
