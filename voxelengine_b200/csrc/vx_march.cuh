@@ -161,6 +161,17 @@ __device__ __forceinline__ void lane_slow(const WorldView& w, Lane& L) {
     lane_step(w, L);
 }
 
+// Occupancy bit of bordered cell idx; the AND and the compare are one LOP3 with a predicate result.
+__device__ __forceinline__ bool cell_bit(const uint32_t* __restrict__ bits, uint32_t idx) {
+    const uint32_t word = __ldg(bits + (idx >> 5));
+    uint32_t p;
+    asm("{\n\t.reg .pred q;\n\t.reg .b32 t, u;\n\t"
+        "shf.r.wrap.b32 t, %1, 0, %2;\n\t"
+        "lop3.or.b32 u|q, t, 1, 0, 0xC0, 0;\n\t" // u = t & 1; q = (u != 0)
+        "selp.u32 %0, 1, 0, q;\n\t}" : "=r"(p) : "r"(word), "r"(idx));
+    return p != 0u;
+}
+
 // Fine level: DDARayTraversal inside one brick (cells = voxels), crossing points tested against [0,factor]^3 before a
 // step is counted (VolumeRaytracer.cu:325-341).  FINE8: factor == 8, mask bit = x + 8y + 64z.
 struct FineOut {
@@ -195,6 +206,42 @@ __device__ __forceinline__ void fine_march(const uint32_t* __restrict__ mask, in
         ++steps;
         o.point = p;
         o.ncode = mx ? (ox ? 1u : 2u) : (my ? (oy ? 3u : 4u) : (oz ? 5u : 6u));
+    }
+    o.steps = steps;
+}
+
+// The same march for the common case: 8^3 brick, start strictly inside [0,8)^3 on every axis that matters (no IsOnEdge
+// padding), no NaN among the tMax values.  Identical arithmetic; what changes is bookkeeping: one range test for the
+// three cell coordinates, the bit index formed directly, the axis chosen by min (ties z over y over x, which is the
+// reference's chain when nothing is NaN), crossing coordinates on the stepped axis taken from the cell faces.
+__device__ __forceinline__ void fine_march8(const uint32_t* __restrict__ mask, V3 s, const Ray& r, FineOut& o) {
+    int cx = (int)s.x, cy = (int)s.y, cz = (int)s.z;
+    const int ox = r.sx > 0, oy = r.sy > 0, oz = r.sz > 0;
+    float tx = r.d.x != 0.0f ? fdiv(fsub((float)(cx + ox), s.x), r.d.x) : CUDART_INF_F;
+    float ty = r.d.y != 0.0f ? fdiv(fsub((float)(cy + oy), s.y), r.d.y) : CUDART_INF_F;
+    float tz = r.d.z != 0.0f ? fdiv(fsub((float)(cz + oz), s.z), r.d.z) : CUDART_INF_F;
+    o.hit = false; o.oob = false; o.point = s; o.ncode = 0; o.cell = 0;
+    int steps = 0;
+    // face coordinate reached when an axis is stepped: (float)(cell + o); it moves by the step sign with the cell
+    float fx = (float)(cx + ox), fy = (float)(cy + oy), fz = (float)(cz + oz);
+    const float sfx = (float)r.sx, sfy = (float)r.sy, sfz = (float)r.sz;
+#pragma unroll 1
+    for (;;) {
+        if ((cx | cy | cz) & ~7) { o.oob = true; break; }
+        const uint32_t bit = (uint32_t)(cx + (cy << 3) + (cz << 6));
+        if (cell_bit(mask, bit)) { o.hit = true; o.cell = (uint32_t)cx | ((uint32_t)cy << 10) | ((uint32_t)cz << 20); break; }
+        const bool mz = tz <= fminf(tx, ty);
+        const bool my = !mz && ty <= tx;
+        const bool mx = !mz && !my;
+        const float t = mz ? tz : (my ? ty : tx);
+        V3 p = mk(fadd(s.x, fmul(t, r.d.x)), fadd(s.y, fmul(t, r.d.y)), fadd(s.z, fmul(t, r.d.z)));
+        if (mz) { p.z = fz; fz = fadd(fz, sfz); tz = fadd(tz, r.dtz); cz += r.sz; }
+        if (my) { p.y = fy; fy = fadd(fy, sfy); ty = fadd(ty, r.dty); cy += r.sy; }
+        if (mx) { p.x = fx; fx = fadd(fx, sfx); tx = fadd(tx, r.dtx); cx += r.sx; }
+        if (fminf(fminf(p.x, p.y), p.z) < 0.0f || fmaxf(fmaxf(p.x, p.y), p.z) > 8.0f) { o.oob = true; break; }
+        ++steps;
+        o.point = p;
+        o.ncode = mz ? (oz ? 5u : 6u) : (my ? (oy ? 3u : 4u) : (ox ? 1u : 2u));
     }
     o.steps = steps;
 }
@@ -249,8 +296,12 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
     if (COUNT) L.work.E++;
     FineOut q;
     const uint32_t* mask = w.pool + (size_t)rec.y * w.words_per_brick;
-    if (w.factor == 8) fine_march<true>(mask, 8, local, r, q);
-    else fine_march<false>(mask, w.factor, local, r, q);
+    if (w.factor == 8) {
+        // fast variant when nothing can be NaN and the start is not on the padded far face (cell == 8 on some axis)
+        const bool plain = (L.flags & F_CAPOK) && (int)local.x != 8 && (int)local.y != 8 && (int)local.z != 8;
+        if (plain) fine_march8(mask, local, r, q);
+        else fine_march<true>(mask, 8, local, r, q);
+    } else fine_march<false>(mask, w.factor, local, r, q);
     L.total += q.steps; L.fsteps += q.steps;
     const V3 hit_pos = mk(fadd(q.point.x, bx), fadd(q.point.y, by), fadd(q.point.z, bz));
     if (q.hit) {
@@ -285,17 +336,6 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
     }
     L.s = start;
     lane_set_state(L, ST_BEGIN);
-}
-
-// Occupancy bit of bordered cell idx; the AND and the compare are one LOP3 with a predicate result.
-__device__ __forceinline__ bool cell_bit(const uint32_t* __restrict__ bits, uint32_t idx) {
-    const uint32_t word = __ldg(bits + (idx >> 5));
-    uint32_t p;
-    asm("{\n\t.reg .pred q;\n\t.reg .b32 t, u;\n\t"
-        "shf.r.wrap.b32 t, %1, 0, %2;\n\t"
-        "lop3.or.b32 u|q, t, 1, 0, 0xC0, 0;\n\t" // u = t & 1; q = (u != 0)
-        "selp.u32 %0, 1, 0, q;\n\t}" : "=r"(p) : "r"(word), "r"(idx));
-    return p != 0u;
 }
 
 // One fast-loop step.  With no NaN among the tMax values (F_CAPOK) the reference's comparison chain (:293-322) picks the
