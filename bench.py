@@ -213,7 +213,14 @@ def run_ours(args, wl, wl_name):
                 dst = frame_b[r::world_size]
                 dst.copy_(recv[r][: dst.shape[0]])
 
-    # counters of exactly this frame (untimed counting variant of the kernel)
+    # counters of exactly this frame (untimed counting variants of the kernels): first the primary rays alone
+    # (shadows off), then the whole frame
+    o_prim = opts(stats.data_ptr())
+    o_prim.shadows = 0
+    render(o_prim)
+    torch.cuda.synchronize()
+    st_prim = stats.clone()
+    stats.zero_()
     render(opts(stats.data_ptr()))
     torch.cuda.synchronize()
     st = stats.clone()
@@ -222,6 +229,13 @@ def run_ours(args, wl, wl_name):
     st = st.cpu().numpy()
     rays = int(st[0] + st[2])
     alg_bytes_rank = int(4 * stats[5].item() + 8 * stats[6].item() + 64 * stats[7].item() + 4 * int(stats[0].item()))
+    # per kernel: primary_rays reads its cells, writes the miss pixels (4 B) or queues the hit (20 B); shadow_rays reads its
+    # lane record (48 B) and cells and writes its result (4 B)
+    p_hits, p_rays = int(st_prim[1].item()), int(st_prim[0].item())
+    alg_primary = int(4 * st_prim[5].item() + 8 * st_prim[6].item() + 64 * st_prim[7].item() + 4 * (p_rays - p_hits) + 20 * p_hits)
+    s_rays = int(stats[2].item())
+    alg_shadow = int(4 * (stats[5] - st_prim[5]).item() + 8 * (stats[6] - st_prim[6]).item() + 64 * (stats[7] - st_prim[7]).item() + 52 * s_rays)
+    rt.set_timing(True)
     o_timed = opts(None)
     for _ in range(max(args.warmup, 3)):
         flush.fill_(1)
@@ -237,6 +251,7 @@ def run_ours(args, wl, wl_name):
     torch.cuda.synchronize()
     wall0 = time.perf_counter()
     k_ms, step_ms = 0.0, 0.0
+    kern_ms = [0.0, 0.0, 0.0, 0.0]
     for _ in range(args.steps):
         flush.fill_(1)  # L2 flush between timed iterations (512 MiB > 126 MB L2)
         e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
@@ -249,14 +264,17 @@ def run_ours(args, wl, wl_name):
         e2.synchronize()
         k_ms += e0.elapsed_time(e1)
         step_ms += e0.elapsed_time(e2)
+        kern_ms = [a + b for a, b in zip(kern_ms, rt.frame_times())]
     torch.cuda.synchronize()
     if world_size > 1:
         dist.barrier()
     wall = time.perf_counter() - wall0
-    t = torch.tensor([step_ms, k_ms], dtype=torch.float64, device="cuda")
+    rt.set_timing(False)
+    t = torch.tensor([step_ms, k_ms] + kern_ms, dtype=torch.float64, device="cuda")
     if world_size > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    step_ms_max, k_ms_max = (float(v) for v in t.cpu())
+    step_ms_max, k_ms_max = (float(v) for v in t.cpu()[:2])
+    kern_ms = [float(v) for v in t.cpu()[2:]]
     clocks = sampler.stop() if sampler else None
 
     # ---- e2e: the reference-facing call with HOST buffers (RenderScreen + cudaMemcpy of main.cu:165-167) ----
@@ -281,7 +299,7 @@ def run_ours(args, wl, wl_name):
     e2e_s = time.perf_counter() - t0
     e2e_rays_s = rays * args.steps / e2e_s / 1e6
     return dict(vx=vx, rank=rank, world_size=world_size, rays=rays, st=st, alg_bytes_rank=alg_bytes_rank, step_ms=step_ms_max,
-                k_ms=k_ms_max, wall=wall, clocks=clocks, e2e=e2e_rays_s, h2d=h2d, d2h=d2h, info=info, cam_pos=cam_pos, world=world,
+                k_ms=k_ms_max, kern_ms=kern_ms, alg_primary=alg_primary, alg_shadow=alg_shadow, wall=wall, clocks=clocks, e2e=e2e_rays_s, h2d=h2d, d2h=d2h, info=info, cam_pos=cam_pos, world=world,
                 rt=rt, dev=dev)
 
 
@@ -332,14 +350,23 @@ def main():
     ms_kernel = res["k_ms"] / K
     value = res["rays"] / (ms_step * 1e-3) / 1e6
     hbm_peak, peak_src = read_peaks()
-    achieved = res["alg_bytes_rank"] / (ms_kernel * 1e-3) / 1e9
-    l2_peak = vx.measure_read_bandwidth(32 << 20, 50, res["dev"])
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             traffic = json.load(f).get(wl_name)
     except Exception:
         pass
+    l2_peak = vx.measure_read_bandwidth(32 << 20, 50, res["dev"])
+    names = vx.VoxelRaytracer3D.KERNELS
+    kern = {n: res["kern_ms"][i] / K for i, n in enumerate(names)}
+
+    def roof(kernel, alg_bytes, formula):
+        ms = kern[kernel]
+        a = alg_bytes / (ms * 1e-3) / 1e9
+        return {"bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s", "frac": a / hbm_peak,
+                "traffic": (traffic or {}).get(kernel) if isinstance(traffic, dict) else None, "peak_source": peak_src,
+                "kernel": "vx::" + kernel, "kernel_ms": ms, "algorithmic_bytes_per_launch": alg_bytes, "formula": formula,
+                "l2_peak_gbs_measured": l2_peak, "frac_of_l2": a / l2_peak}
     st = res["st"]
     line = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": res["world_size"], "steps": K, "warmup": max(args.warmup, 3),
@@ -351,11 +378,12 @@ def main():
                              "pool_mb": res["info"].bytes_pool / 1e6, "build_ms": res["info"].build_ms}},
         "clocks": res["clocks"],
         "e2e": {"value": res["e2e"], "unit": "Mrays/s", "h2d_bytes_per_step": res["h2d"], "d2h_bytes_per_step": res["d2h"]},
-        "gpu_launches": K,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
-                     "peak_source": peak_src, "kernel": "vx::render_frame", "kernel_ms": ms_kernel,
-                     "algorithmic_bytes_per_launch": res["alg_bytes_rank"], "formula": "4*C + 8*K + 64*E + 4*pixels (SURVEY.md 8d)",
-                     "l2_peak_gbs_measured": l2_peak, "frac_of_l2": achieved / l2_peak},
+        "gpu_launches": 4 * K,
+        "kernels_ms": dict(kern, frame=ms_kernel),
+        # the dominant kernel first; the sun-ray march, the other half of the frame, beside it
+        "roofline": roof("primary_rays", res["alg_primary"], "4*C + 8*K + 64*E of the primary rays + 4 B per miss pixel + 20 B per queued hit (SURVEY.md 8d)"),
+        "roofline_shadow_rays": roof("shadow_rays", res["alg_shadow"], "4*C + 8*K + 64*E of the sun rays + 48 B lane record + 4 B result per ray"),
+        "frame_algorithmic_bytes": res["alg_bytes_rank"],
         "wall_s_timed_region": res["wall"],
     }
     if res["world_size"] == 1 and not args.no_cpu_baseline:

@@ -161,6 +161,14 @@ int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_re
 int vx_render_host(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* opts,
                    void* h_bgra, uint32_t W, uint32_t H);
 
+/* Per-kernel device times of a frame.  A frame is up to four launches on `stream`: primary_rays (march of the
+ * primary rays; misses and unshadowed modes write their pixels), then with shadows on shadow_setup, shadow_rays (march
+ * of the sun rays of Renderer.cu:102) and shade_pixels.  After vx_tracer_set_timing(t, 1) every vx_render records CUDA
+ * events around them; vx_tracer_frame_times waits for the last frame and returns the four durations in ms (0 for
+ * launches the frame did not need). */
+int vx_tracer_set_timing(vx_tracer* t, int enable);
+int vx_tracer_frame_times(vx_tracer* t, float ms[4]);
+
 /* Device math the parity harness shares with the CPU oracle. */
 int vx_device_tanf(float x, float* out, int device);
 int vx_device_normalize(const float* dirs_xyz, float* out_xyz, size_t n, int device); /* device rsqrtf */

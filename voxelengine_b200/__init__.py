@@ -65,7 +65,7 @@ ABI_SYMBOLS = [
     "vx_last_error", "vx_version", "vx_device_count", "vx_world_build_noise", "vx_world_build_noise_full",
     "vx_world_from_dense_bits", "vx_world_destroy", "vx_world_get_info", "vx_world_download", "vx_tracer_create",
     "vx_tracer_destroy", "vx_trace", "vx_trace_device", "vx_hits_postprocess", "vx_get_directions", "vx_render",
-    "vx_render_host", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
+    "vx_render_host", "vx_tracer_set_timing", "vx_tracer_frame_times", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
 ]
 
 _lib = None
@@ -269,6 +269,18 @@ class VoxelRaytracer3D:
     def render_device(self, cam, env, opts, d_bgra, W, H, d_steps=0, stream=0):
         _check(lib().vx_render(self.h, C.byref(cam), C.byref(env), C.byref(opts), int(d_bgra), int(d_steps) or None, W, H,
                                int(stream) or None))
+
+    KERNELS = ("primary_rays", "shadow_setup", "shadow_rays", "shade_pixels")
+
+    def set_timing(self, enable=True):
+        """Record CUDA events around the launches of every following frame (vx_tracer_set_timing)."""
+        _check(lib().vx_tracer_set_timing(self.h, 1 if enable else 0))
+
+    def frame_times(self):
+        """Device ms of the last frame's launches, in KERNELS order (waits for the frame)."""
+        ms = (C.c_float * 4)()
+        _check(lib().vx_tracer_frame_times(self.h, ms))
+        return [float(v) for v in ms]
 
     def render_host(self, cam, env, opts, W, H, bgra=None):
         if bgra is None:

@@ -388,6 +388,7 @@ extern "C" int vx_tracer_destroy(vx_tracer* t) {
     cudaFree(t->d_origins); cudaFree(t->d_dirs); cudaFree(t->d_hit); cudaFree(t->d_pos); cudaFree(t->d_normal);
     cudaFree(t->d_steps); cudaFree(t->d_voxel); cudaFree(t->d_brick); cudaFree(t->d_csteps); cudaFree(t->d_fsteps);
     cudaFree(t->d_counters); cudaFree(t->d_frame); cudaFree(t->d_next); cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux); cudaFree(t->d_queue_lanes);
+    for (int i = 0; i < 5; ++i) if (t->ev[i]) cudaEventDestroy(t->ev[i]);
     if (t->stream) cudaStreamDestroy(t->stream);
     delete t;
     return VX_OK;
@@ -601,17 +602,45 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     if (shadow_pass) { rc = next_counter(t, cs, &next2); if (rc) return rc; }
     unsigned blocks = 1;
     const unsigned dense_blocks = (unsigned)(t->sm_count > 0 ? t->sm_count : 148) * 8u; // grid-stride over a device-side count
+    // optional per-kernel timing (vx_tracer_set_timing): events between the launches, on the launching stream
+#define VX_MARK(i) do { if (t->timing) VX_CUDA(cudaEventRecord(t->ev[i], cs)); } while (0)
+    t->timed_kernels = 0;
 #define VX_LAUNCH(N, S) do { rc = persistent_blocks(t, primary_rays<N, S>, f.ids, blocks); if (rc) return rc; \
+        VX_MARK(0); \
         primary_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); \
+        VX_MARK(1); t->timed_kernels = 1; \
         if (shadow_pass) { \
             shadow_setup<N><<<dense_blocks, 256, 0, cs>>>(w, f, q); \
+            VX_MARK(2); \
             rc = persistent_blocks(t, shadow_rays<N, S>, f.ids, blocks); if (rc) return rc; \
             shadow_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, q, next2); \
-            shade_pixels<N, S><<<dense_blocks, 256, 0, cs>>>(f, (uint8_t*)d_bgra, d_steps, st, q); } } while (0)
+            VX_MARK(3); \
+            shade_pixels<N, S><<<dense_blocks, 256, 0, cs>>>(f, (uint8_t*)d_bgra, d_steps, st, q); \
+            VX_MARK(4); t->timed_kernels = 4; } } while (0)
     if (opts->norm_mode == VX_NORM_HOST) { if (st) VX_LAUNCH(1, true); else VX_LAUNCH(1, false); }
     else { if (st) VX_LAUNCH(0, true); else VX_LAUNCH(0, false); }
 #undef VX_LAUNCH
+#undef VX_MARK
     VX_CUDA(cudaGetLastError());
+    return VX_OK;
+}
+
+extern "C" int vx_tracer_set_timing(vx_tracer* t, int enable) {
+    VX_REQUIRE(t != nullptr, "NULL argument");
+    DeviceGuard guard(t->device);
+    if (enable && !t->ev[0]) for (int i = 0; i < 5; ++i) VX_CUDA(cudaEventCreate(&t->ev[i]));
+    t->timing = enable != 0;
+    t->timed_kernels = 0;
+    return VX_OK;
+}
+
+extern "C" int vx_tracer_frame_times(vx_tracer* t, float ms[4]) {
+    VX_REQUIRE(t && ms, "NULL argument");
+    VX_REQUIRE(t->timing && t->timed_kernels > 0, "no timed frame: call vx_tracer_set_timing(t, 1) and render first");
+    DeviceGuard guard(t->device);
+    for (int i = 0; i < 4; ++i) ms[i] = 0.0f;
+    VX_CUDA(cudaEventSynchronize(t->ev[t->timed_kernels]));
+    for (int i = 0; i < t->timed_kernels; ++i) VX_CUDA(cudaEventElapsedTime(&ms[i], t->ev[i], t->ev[i + 1]));
     return VX_OK;
 }
 
