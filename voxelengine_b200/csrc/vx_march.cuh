@@ -220,30 +220,35 @@ __device__ __forceinline__ void fine_march8(const uint32_t* __restrict__ mask, V
     float tx = r.d.x != 0.0f ? fdiv(fsub((float)(cx + ox), s.x), r.d.x) : CUDART_INF_F;
     float ty = r.d.y != 0.0f ? fdiv(fsub((float)(cy + oy), s.y), r.d.y) : CUDART_INF_F;
     float tz = r.d.z != 0.0f ? fdiv(fsub((float)(cz + oz), s.z), r.d.z) : CUDART_INF_F;
-    o.hit = false; o.oob = false; o.point = s; o.ncode = 0; o.cell = 0;
+    V3 point = s;
+    uint32_t ncode = 0;
     int steps = 0;
-    // face coordinate reached when an axis is stepped: (float)(cell + o); it moves by the step sign with the cell
-    float fx = (float)(cx + ox), fy = (float)(cy + oy), fz = (float)(cz + oz);
-    const float sfx = (float)r.sx, sfy = (float)r.sy, sfz = (float)r.sz;
+    // The exits are labels so that the outcome flags are set once, after the loop, instead of being carried through it.
 #pragma unroll 1
     for (;;) {
-        if ((cx | cy | cz) & ~7) { o.oob = true; break; }
-        const uint32_t bit = (uint32_t)(cx + (cy << 3) + (cz << 6));
-        if (cell_bit(mask, bit)) { o.hit = true; o.cell = (uint32_t)cx | ((uint32_t)cy << 10) | ((uint32_t)cz << 20); break; }
+        if ((cx | cy | cz) & ~7) goto out_of_brick;
+        if (cell_bit(mask, (uint32_t)(cx + (cy << 3) + (cz << 6)))) goto hit_voxel;
         const bool mz = tz <= fminf(tx, ty);
         const bool my = !mz && ty <= tx;
         const bool mx = !mz && !my;
         const float t = mz ? tz : (my ? ty : tx);
         V3 p = mk(fadd(s.x, fmul(t, r.d.x)), fadd(s.y, fmul(t, r.d.y)), fadd(s.z, fmul(t, r.d.z)));
-        if (mz) { p.z = fz; fz = fadd(fz, sfz); tz = fadd(tz, r.dtz); cz += r.sz; }
-        if (my) { p.y = fy; fy = fadd(fy, sfy); ty = fadd(ty, r.dty); cy += r.sy; }
-        if (mx) { p.x = fx; fx = fadd(fx, sfx); tx = fadd(tx, r.dtx); cx += r.sx; }
-        if (fminf(fminf(p.x, p.y), p.z) < 0.0f || fmaxf(fmaxf(p.x, p.y), p.z) > 8.0f) { o.oob = true; break; }
+        // on the stepped axis the crossing is the face of the cell being left: (float)(cell + o)
+        if (mz) { p.z = (float)(cz + oz); tz = fadd(tz, r.dtz); cz += r.sz; }
+        if (my) { p.y = (float)(cy + oy); ty = fadd(ty, r.dty); cy += r.sy; }
+        if (mx) { p.x = (float)(cx + ox); tx = fadd(tx, r.dtx); cx += r.sx; }
+        if (fminf(fminf(p.x, p.y), p.z) < 0.0f || fmaxf(fmaxf(p.x, p.y), p.z) > 8.0f) goto out_of_brick;
         ++steps;
-        o.point = p;
-        o.ncode = mz ? (oz ? 5u : 6u) : (my ? (oy ? 3u : 4u) : (ox ? 1u : 2u));
+        point = p;
+        ncode = mz ? (oz ? 5u : 6u) : (my ? (oy ? 3u : 4u) : (ox ? 1u : 2u));
     }
-    o.steps = steps;
+hit_voxel:
+    o.hit = true; o.oob = false; o.cell = (uint32_t)cx | ((uint32_t)cy << 10) | ((uint32_t)cz << 20);
+    o.point = point; o.ncode = ncode; o.steps = steps;
+    return;
+out_of_brick:
+    o.hit = false; o.oob = true; o.cell = 0;
+    o.point = point; o.ncode = ncode; o.steps = steps;
 }
 
 // ST_CAND: the occupied cell L.bidx.  Tight-AABB slab test (VolumeRaytracer.cu:248-273); on a hit the brick is
@@ -294,6 +299,13 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
     const float bx = fmul((float)qx, ff), by = fmul((float)qy, ff), bz = fmul((float)qz, ff);
     const V3 local = mk(fsub(fmul(point.x, ff), bx), fsub(fmul(point.y, ff), by), fsub(fmul(point.z, ff), bz));
     if (COUNT) L.work.E++;
+    // Axis of the coarse traversal's next advance (its NextCell, :347): the only thing the re-seeding below may still need
+    // from the coarse state.  tMax and the cell index are dead from here on (every way out of this function that marches
+    // again goes through lane_begin), and saying so keeps them out of registers during the brick march.
+    const bool nmx = L.tx < L.ty && L.tx < L.tz;
+    const bool nmy = !nmx && L.ty <= L.tx && L.ty < L.tz;
+    const uint32_t next_axis = nmx ? 0u : (nmy ? 1u : 2u);
+    L.tx = L.ty = L.tz = 0.0f; L.idx = 0;
     FineOut q;
     const uint32_t* mask = w.pool + (size_t)rec.y * w.words_per_brick;
     if (w.factor == 8) {
@@ -323,10 +335,7 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
         start.z = nextafterf(start.z, L.d.z < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
         if (qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) {
             // NextCell of the COARSE traversal = the cell after its final advance (:347, :473)
-            const bool mx = L.tx < L.ty && L.tx < L.tz;
-            const bool my = !mx && L.ty <= L.tx && L.ty < L.tz;
-            const bool mz = !mx && !my;
-            const int nx = cx + (mx ? r.sx : 0), ny = cy + (my ? r.sy : 0), nz = cz + (mz ? r.sz : 0);
+            const int nx = cx + (next_axis == 0u ? r.sx : 0), ny = cy + (next_axis == 1u ? r.sy : 0), nz = cz + (next_axis == 2u ? r.sz : 0);
             const float gx = fsub((float)nx, start.x), gy = fsub((float)ny, start.y), gz = fsub((float)nz, start.z);
             const float ax = fabsf(gx), ay = fabsf(gy), az = fabsf(gz);
             if (ax < ay && ax < az) start.x = fadd(start.x, gx);
@@ -363,6 +372,7 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 // Warp driver.  `Policy` supplies the rays and consumes the results:
 //   uint64_t count()                      rays (ids) in this launch
 //   int max_steps()
+//   void prepare(L)                       once per thread before any ray (e.g. a direction common to all rays)
 //   void init(w, id, L)                   set the lane up for ray `id` (lane_setup) or leave it ST_IDLE
 //   void finish(w, L, pos, ncode)         consume a finished march and set the lane ST_IDLE (or re-arm it)
 //   kRefill                               idle lanes that trigger a refill (32: whole tiles only)
@@ -392,6 +402,7 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
     L.d = mk(0.0f, 0.0f, 0.0f); L.ivx = L.ivy = L.ivz = 0.0f; L.s = L.d; L.tx = L.ty = L.tz = 0.0f;
     L.idx = 0; L.bidx = 0; L.pc = kNoCell; L.flags = ST_IDLE; L.total = 0; L.csteps = L.fsteps = 0; L.fcell = 0;
     L.work.C = L.work.K = L.work.E = 0;
+    pol.prepare(L); // policies whose rays share one direction set it here, once, so it never becomes per-lane state
     unsigned long long cur = 0, end = 0;
     bool exhausted = false;
     for (;;) {

@@ -31,6 +31,7 @@ struct BatchPolicy {
 
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return cap; }
+    __device__ __forceinline__ void prepare(Lane&) {}
     __device__ __forceinline__ void init(const WorldView& w, unsigned long long i, Lane& L) {
         id = i;
         const float ff = (float)w.factor;
@@ -194,6 +195,7 @@ struct PrimaryPolicy {
         : f(fp), bgra(b), steps_plane(sp), stats(st), q(sq), pix(0) {}
     __device__ __forceinline__ unsigned long long count() const { return f.ids; }
     __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
+    __device__ __forceinline__ void prepare(Lane&) {}
 
     // getRayDirection, Renderer.cu:44-59
     __device__ __forceinline__ V3 primary_dir(int x, int y) const {
@@ -287,21 +289,21 @@ struct ShadowPolicy {
     const FrameParams& f;
     ShadowQueue q;
     unsigned long long n;
-    V3 d; float ivx, ivy, ivz; // the same for every sun ray
     uint32_t slot;             // per lane: queue entry whose sun ray this lane marches
 
-    __device__ __forceinline__ ShadowPolicy(const FrameParams& fp, ShadowQueue sq) : f(fp), q(sq), n(*sq.count), slot(0) {
-        V3 once;
-        d = sun_direction<NORM>(f, once);
-        ivx = fdiv(1.0f, d.x == 0.0f ? kFltEps : d.x); ivy = fdiv(1.0f, d.y == 0.0f ? kFltEps : d.y); ivz = fdiv(1.0f, d.z == 0.0f ? kFltEps : d.z);
-    }
+    __device__ __forceinline__ ShadowPolicy(const FrameParams& fp, ShadowQueue sq) : f(fp), q(sq), n(*sq.count), slot(0) {}
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
+    __device__ __forceinline__ void prepare(Lane& L) { // direction and slab inverses are the same for every sun ray
+        V3 once;
+        L.d = sun_direction<NORM>(f, once);
+        L.ivx = fdiv(1.0f, L.d.x == 0.0f ? kFltEps : L.d.x); L.ivy = fdiv(1.0f, L.d.y == 0.0f ? kFltEps : L.d.y);
+        L.ivz = fdiv(1.0f, L.d.z == 0.0f ? kFltEps : L.d.z);
+    }
 
     __device__ __forceinline__ void init(const WorldView&, unsigned long long id, Lane& L) {
         slot = (uint32_t)id;
         const uint4 a = q.lanes[3 * id], b = q.lanes[3 * id + 1], c = q.lanes[3 * id + 2];
-        L.d = d; L.ivx = ivx; L.ivy = ivy; L.ivz = ivz;
         L.s = mk(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z));
         L.tx = __uint_as_float(a.w); L.ty = __uint_as_float(b.x); L.tz = __uint_as_float(b.y);
         L.idx = b.z; L.total = 0; L.pc = c.x; L.flags = c.y;
