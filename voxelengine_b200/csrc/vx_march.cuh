@@ -221,34 +221,66 @@ __device__ __forceinline__ void fine_march8(const uint32_t* __restrict__ mask, V
     float ty = r.d.y != 0.0f ? fdiv(fsub((float)(cy + oy), s.y), r.d.y) : CUDART_INF_F;
     float tz = r.d.z != 0.0f ? fdiv(fsub((float)(cz + oz), s.z), r.d.z) : CUDART_INF_F;
     V3 point = s;
-    uint32_t ncode = 0;
+    uint32_t axis = 3u; // axis of the last counted step (3: none yet)
     int steps = 0;
+    float dtx = r.dtx, dty = r.dty, dtz = r.dtz;
+    int sx = r.sx, sy = r.sy, sz = r.sz;
+#ifndef VX_FINE_NO_PIN
+    // keep the loop invariants in registers: left alone, the compiler re-derives them from the direction in every round
+    asm volatile("" : "+f"(dtx), "+f"(dty), "+f"(dtz), "+r"(sx), "+r"(sy), "+r"(sz), "+l"(mask));
+#endif
     // The exits are labels so that the outcome flags are set once, after the loop, instead of being carried through it.
 #pragma unroll 1
     for (;;) {
         if ((cx | cy | cz) & ~7) goto out_of_brick;
         if (cell_bit(mask, (uint32_t)(cx + (cy << 3) + (cz << 6)))) goto hit_voxel;
-        const bool mz = tz <= fminf(tx, ty);
-        const bool my = !mz && ty <= tx;
-        const bool mx = !mz && !my;
-        const float t = mz ? tz : (my ? ty : tx);
-        V3 p = mk(fadd(s.x, fmul(t, r.d.x)), fadd(s.y, fmul(t, r.d.y)), fadd(s.z, fmul(t, r.d.z)));
-        // on the stepped axis the crossing is the face of the cell being left: (float)(cell + o)
-        if (mz) { p.z = (float)(cz + oz); tz = fadd(tz, r.dtz); cz += r.sz; }
-        if (my) { p.y = (float)(cy + oy); ty = fadd(ty, r.dty); cy += r.sy; }
-        if (mx) { p.x = (float)(cx + ox); tx = fadd(tx, r.dtx); cx += r.sx; }
-        if (fminf(fminf(p.x, p.y), p.z) < 0.0f || fmaxf(fmaxf(p.x, p.y), p.z) > 8.0f) goto out_of_brick;
+        float px, py, pz;
+        uint32_t ax;
+        // One step: axis of the minimum tMax (ties z over y over x), crossing point = start + t * direction except on the
+        // stepped axis, where it is the face of the cell being left, (float)(cell + o); then tMax and the cell advance.
+        asm("{\n\t.reg .pred qz, qy, qx;\n\t.reg .f32 m, t;\n\t.reg .s32 c;\n\t"
+            "min.f32 m, %0, %1;\n\t"
+            "setp.le.f32 qz, %2, m;\n\t"
+            "setp.le.and.f32 qy, %1, %0, !qz;\n\t"
+            "setp.gt.and.f32 qx, %1, %0, !qz;\n\t"
+            "selp.f32 t, %1, %0, qy;\n\t"
+            "selp.f32 t, %2, t, qz;\n\t"
+            "selp.u32 %9, 1, 0, qy;\n\t"
+            "selp.u32 %9, 2, %9, qz;\n\t"
+            "mul.rn.f32 %6, t, %13;\n\t"
+            "mul.rn.f32 %7, t, %14;\n\t"
+            "mul.rn.f32 %8, t, %15;\n\t"
+            "add.rn.f32 %6, %10, %6;\n\t"
+            "add.rn.f32 %7, %11, %7;\n\t"
+            "add.rn.f32 %8, %12, %8;\n\t"
+            "@qz add.s32 c, %5, %24;\n\t"
+            "@qz cvt.rn.f32.s32 %8, c;\n\t"
+            "@qz add.rn.f32 %2, %2, %18;\n\t"
+            "@qz add.s32 %5, %5, %21;\n\t"
+            "@qy add.s32 c, %4, %23;\n\t"
+            "@qy cvt.rn.f32.s32 %7, c;\n\t"
+            "@qy add.rn.f32 %1, %1, %17;\n\t"
+            "@qy add.s32 %4, %4, %20;\n\t"
+            "@qx add.s32 c, %3, %22;\n\t"
+            "@qx cvt.rn.f32.s32 %6, c;\n\t"
+            "@qx add.rn.f32 %0, %0, %16;\n\t"
+            "@qx add.s32 %3, %3, %19;\n\t}"
+            : "+f"(tx), "+f"(ty), "+f"(tz), "+r"(cx), "+r"(cy), "+r"(cz), "=f"(px), "=f"(py), "=f"(pz), "=r"(ax)
+            : "f"(s.x), "f"(s.y), "f"(s.z), "f"(r.d.x), "f"(r.d.y), "f"(r.d.z), "f"(dtx), "f"(dty), "f"(dtz), "r"(sx), "r"(sy), "r"(sz),
+              "r"(ox), "r"(oy), "r"(oz));
+        if (fminf(fminf(px, py), pz) < 0.0f || fmaxf(fmaxf(px, py), pz) > 8.0f) goto out_of_brick;
         ++steps;
-        point = p;
-        ncode = mz ? (oz ? 5u : 6u) : (my ? (oy ? 3u : 4u) : (ox ? 1u : 2u));
+        point = mk(px, py, pz);
+        axis = ax;
     }
 hit_voxel:
     o.hit = true; o.oob = false; o.cell = (uint32_t)cx | ((uint32_t)cy << 10) | ((uint32_t)cz << 20);
-    o.point = point; o.ncode = ncode; o.steps = steps;
-    return;
+    goto done;
 out_of_brick:
     o.hit = false; o.oob = true; o.cell = 0;
-    o.point = point; o.ncode = ncode; o.steps = steps;
+done:
+    o.point = point; o.steps = steps;
+    o.ncode = axis == 3u ? 0u : (axis == 2u ? (oz ? 5u : 6u) : (axis == 1u ? (oy ? 3u : 4u) : (ox ? 1u : 2u)));
 }
 
 // ST_CAND: the occupied cell L.bidx.  Tight-AABB slab test (VolumeRaytracer.cu:248-273); on a hit the brick is
