@@ -209,3 +209,33 @@ def test_full_scale_frame_matches_oracle(vx):
         assert diff.max() <= 1
         assert gsteps.mean() > 5
     probe.close(); rt.close(); w.close()
+
+
+def test_bands_and_tiles_compose_the_full_frame(vx, gpu_worlds):
+    """Multi-GPU partition, device side: rendering the bands of every rank (vx_render_opts.band_count/band_index), or a set
+    of tile rectangles, into one buffer gives the same bytes and steps as rendering the whole frame at once."""
+    import torch
+    dims, org = (128, 64, 128), (512, 0, 256)
+    w = gpu_worlds(dims, org, 8)
+    W, H = 200, 117  # not a multiple of the 16x8 macro tile
+    cam = vx.make_camera((64, 90, 150), (-0.45, 0.3, 0.0), 90.0)
+    rt = vx.VoxelRaytracer3D(w, 1)
+
+    def render(**kw):
+        frame = torch.full((H, W, 4), 7, dtype=torch.uint8, device="cuda")
+        steps = torch.full((H, W), -1, dtype=torch.int32, device="cuda")
+        for o in kw["passes"]:
+            rt.render_device(cam, vx.default_env(), o, frame.data_ptr(), W, H, d_steps=steps.data_ptr())
+        torch.cuda.synchronize()
+        return frame.cpu().numpy(), steps.cpu().numpy()
+
+    for cb in (0, 1):
+        whole = render(passes=[vx.RenderOpts(cb, 2, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None)])
+        for n in (2, 3, 8):
+            banded = render(passes=[vx.RenderOpts(cb, 2, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None, n, r) for r in range(n)])
+            assert np.array_equal(whole[0], banded[0]) and np.array_equal(whole[1], banded[1]), "bands x%d, checkerboard %d" % (n, cb)
+        rows = H // 2 if cb else H
+        tiles = [(x0, y0, 96, 40) for y0 in range(0, rows, 40) for x0 in range(0, 224, 96)]  # thread-space rectangles
+        tiled = render(passes=[vx.RenderOpts(cb, 2, 0, 1, 1, vx.NORM_DEVICE, x0, y0, tw, th, None) for (x0, y0, tw, th) in tiles])
+        assert np.array_equal(whole[0], tiled[0]) and np.array_equal(whole[1], tiled[1]), "tiles, checkerboard %d" % cb
+    rt.close()
