@@ -161,6 +161,16 @@ int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_re
 int vx_render_host(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* opts,
                    void* h_bgra, uint32_t W, uint32_t H);
 
+/* Incoherent secondary rays (BASELINE config 5).  For every primary hit of the frame (cam, opts: checkerboard, frame_number,
+ * tile/band fields and norm_mode are honoured) generates the ambient-occlusion sample ray of calculateColor's sample loop
+ * (Renderer.cu:121-165, sample i = 0): seed = thread_y * W + thread_x + (frame_number + 1) * 1000, direction =
+ * normalize(randomFloat(seed, seed*10, seed*100) * 2 - 1) reflected into the hemisphere of the shading normal, origin = hit
+ * position + normal * 0.01.  Device outputs with room for W*H rays: origins xyz, directions xyz, pixel index y*W+x, and the
+ * ray count (one u64).  Ray order follows the frame's hit queue and is not deterministic; `pixels` identifies the rays.
+ * Trace them with vx_trace_device (the reference passes maxSteps = 8 here; config 5 uses the full cap). */
+int vx_bounce_rays(vx_tracer* t, const vx_camera* cam, const vx_render_opts* opts, uint32_t W, uint32_t H,
+                   float* d_origins_xyz, float* d_dirs_xyz, uint32_t* d_pixels, unsigned long long* d_count, void* stream);
+
 /* Per-kernel device times of a frame.  A frame is up to four launches on `stream`: primary_rays (march of the
  * primary rays; misses and unshadowed modes write their pixels), then with shadows on shadow_setup, shadow_rays (march
  * of the sun rays of Renderer.cu:102) and shade_pixels.  After vx_tracer_set_timing(t, 1) every vx_render records CUDA

@@ -239,3 +239,90 @@ def test_bands_and_tiles_compose_the_full_frame(vx, gpu_worlds):
         tiled = render(passes=[vx.RenderOpts(cb, 2, 0, 1, 1, vx.NORM_DEVICE, x0, y0, tw, th, None) for (x0, y0, tw, th) in tiles])
         assert np.array_equal(whole[0], tiled[0]) and np.array_equal(whole[1], tiled[1]), "tiles, checkerboard %d" % cb
     rt.close()
+
+
+def _host_normalize(v):
+    """normalize() with CUDA's host rsqrtf: (float)(1.0 / sqrt((double)dot)), dot in float32 left to right."""
+    v = v.astype(np.float32)
+    d = (v[:, 0] * v[:, 0] + v[:, 1] * v[:, 1]).astype(np.float32) + (v[:, 2] * v[:, 2]).astype(np.float32)
+    inv = (1.0 / np.sqrt(d.astype(np.float64))).astype(np.float32)
+    return (v * inv[:, None]).astype(np.float32)
+
+
+def _noise_hash(seed):
+    s = seed.astype(np.uint32)
+    with np.errstate(over="ignore"):
+        s = (s + np.uint32(0x7ed55d16)) + (s << np.uint32(12))
+        s = (s ^ np.uint32(0xc761c23c)) ^ (s >> np.uint32(19))
+        s = (s + np.uint32(0x165667b1)) + (s << np.uint32(5))
+        s = (s + np.uint32(0xd3a2646c)) ^ (s << np.uint32(9))
+        s = (s + np.uint32(0xfd7046c5)) + (s << np.uint32(3))
+        s = (s ^ np.uint32(0xb55a4f09)) ^ (s >> np.uint32(16))
+    return s
+
+
+@pytest.mark.parametrize("checkerboard,frame", [(0, 0), (1, 3)])
+def test_bounce_rays_match_reference_sample_loop(vx, gpu_worlds, checkerboard, frame):
+    """BASELINE config 5: the AO sample ray of Renderer.cu:121-165 for every primary hit.  Generation is checked against
+    a numpy restatement (hash, randomFloat, hemisphere flip, origin offset) fed with the primary hits of the batch API;
+    the incoherent rays are then traced on the GPU and by the oracle: every plane identical."""
+    import torch
+    from raysets import camera_rays
+    dims, org = (128, 64, 128), (512, 0, 256)
+    w = gpu_worlds(dims, org, 8)
+    ow = worlds.oracle_world(dims, org, 8)
+    W, H = 256, 144
+    tan_half = vx.device_tanf(np.float32(np.float32(90.0 * 3.1415 / 180.0) / np.float32(2.0)))
+    euler, cam_pos = (-0.45, 0.3, 0.0), (64, 90, 150)
+    cam = vx.make_camera(cam_pos, euler, 90.0)
+    rt = vx.VoxelRaytracer3D(w, W * H)
+    opts = vx.RenderOpts(checkerboard, frame, 0, 1, 1, vx.NORM_HOST, 0, 0, 0, 0, None)
+    d_o = torch.zeros(W * H * 3, dtype=torch.float32, device="cuda")
+    d_d = torch.zeros(W * H * 3, dtype=torch.float32, device="cuda")
+    d_p = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    d_n = torch.zeros(1, dtype=torch.int64, device="cuda")
+    rt.bounce_rays(cam, opts, W, H, d_o.data_ptr(), d_d.data_ptr(), d_p.data_ptr(), d_n.data_ptr())
+    torch.cuda.synchronize()
+    n = int(d_n.item())
+    order = np.argsort(d_p[:n].cpu().numpy())
+    pix = d_p[:n].cpu().numpy()[order]
+    bo = d_o[:3 * n].cpu().numpy().reshape(-1, 3)[order]
+    bd = d_d[:3 * n].cpu().numpy().reshape(-1, 3)[order]
+    assert n > 1000 and len(np.unique(pix)) == n
+
+    # expected: primary rays of the written pixels through the batch API, then the sample loop in numpy
+    fwd, up, right = [np.array(v, np.float32) for v in (cam.fwd, cam.up, cam.right)]
+    po, pd = camera_rays(cam_pos, fwd, up, right, W, H, tan_half)
+    prim = rt.raytrace(po, _host_normalize(pd), norm_mode=vx.NORM_HOST)
+    ys, xs = np.divmod(np.arange(W * H), W)
+    if checkerboard:  # thread (tx, ty) -> pixel (x, 2 ty + (x even) + (frame even)); other pixels are not rendered
+        adj = (xs % 2 == 0).astype(np.int64) + (1 if frame % 2 == 0 else 0)
+        rendered = ((ys - adj) >= 0) & ((ys - adj) % 2 == 0) & ((ys - adj) // 2 < H // 2)
+        tys = (ys - adj) // 2
+    else:
+        rendered, tys = np.ones(W * H, bool), ys
+    sel = np.nonzero(rendered & prim["hit"].astype(bool))[0]
+    assert np.array_equal(sel, pix), "bounce rays must exist exactly for the rendered primary hits"
+    nrm = (-prim["normal"][sel]).astype(np.float32)
+    with np.errstate(over="ignore"):
+        si = (tys[sel] * W + xs[sel] + (frame + 1) * 1000).astype(np.int32)
+        r = [(_noise_hash((si * np.int32(k)).astype(np.int32).view(np.uint32)).astype(np.float32) / np.float32(0xffffffff)) for k in (1, 10, 100)]
+    sd = _host_normalize(np.stack([v * np.float32(2) - np.float32(1) for v in r], 1))
+
+    def dot(a, b):
+        return ((a[:, 0] * b[:, 0] + a[:, 1] * b[:, 1]).astype(np.float32) + a[:, 2] * b[:, 2]).astype(np.float32)
+    flip = dot(sd, nrm) < 0
+    dn = dot(nrm, sd)
+    refl = (sd - ((np.float32(2) * nrm).astype(np.float32) * dn[:, None]).astype(np.float32)).astype(np.float32)
+    sd = np.where(flip[:, None], refl, sd)
+    eo = (prim["pos"][sel] + (nrm * np.float32(0.01)).astype(np.float32)).astype(np.float32)
+    assert np.array_equal(bd.view(np.uint32), sd.view(np.uint32)), "sample directions differ"
+    assert np.array_equal(bo.view(np.uint32), eo.view(np.uint32)), "sample origins differ"
+
+    got = rt.raytrace(bo, bd, norm_mode=vx.NORM_HOST, counters=True)
+    ref = ow.trace(bo, bd, norm_mode=ol.NORM_HOST)
+    assert_same_hits(got, ref, counters=True)
+    got8 = rt.raytrace(bo, bd, norm_mode=vx.NORM_HOST, max_steps=8)  # the cap the reference passes (Renderer.cu:143)
+    ref8 = ow.trace(bo, bd, norm_mode=ol.NORM_HOST, max_steps=8)
+    assert_same_hits(got8, ref8)
+    rt.close()

@@ -65,7 +65,7 @@ ABI_SYMBOLS = [
     "vx_last_error", "vx_version", "vx_device_count", "vx_world_build_noise", "vx_world_build_noise_full",
     "vx_world_from_dense_bits", "vx_world_destroy", "vx_world_get_info", "vx_world_download", "vx_tracer_create",
     "vx_tracer_destroy", "vx_trace", "vx_trace_device", "vx_hits_postprocess", "vx_get_directions", "vx_render",
-    "vx_render_host", "vx_tracer_set_timing", "vx_tracer_frame_times", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
+    "vx_render_host", "vx_bounce_rays", "vx_tracer_set_timing", "vx_tracer_frame_times", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
 ]
 
 _lib = None
@@ -98,6 +98,9 @@ def lib():
     L.vx_get_directions.restype = None
     L.vx_render.argtypes = [vp, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts), vp, vp, u32, u32, vp]
     L.vx_render_host.argtypes = [vp, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts), vp, u32, u32]
+    L.vx_bounce_rays.argtypes = [vp, C.POINTER(Camera), C.POINTER(RenderOpts), u32, u32, vp, vp, vp, vp, vp]
+    L.vx_tracer_set_timing.argtypes = [vp, i32]
+    L.vx_tracer_frame_times.argtypes = [vp, C.POINTER(C.c_float * 4)]
     L.vx_device_tanf.argtypes = [C.c_float, C.POINTER(C.c_float), i32]
     L.vx_device_normalize.argtypes = [vp, vp, sz, i32]
     L.vx_measure_read_bandwidth.argtypes = [i32, sz, i32, C.POINTER(C.c_float)]
@@ -270,6 +273,11 @@ class VoxelRaytracer3D:
         _check(lib().vx_render(self.h, C.byref(cam), C.byref(env), C.byref(opts), int(d_bgra), int(d_steps) or None, W, H,
                                int(stream) or None))
 
+    def bounce_rays(self, cam, opts, W, H, d_origins, d_dirs, d_pixels, d_count, stream=0):
+        """vx_bounce_rays: the AO sample ray of every primary hit of the frame, into device arrays (pointers as ints)."""
+        _check(lib().vx_bounce_rays(self.h, C.byref(cam), C.byref(opts), W, H, int(d_origins), int(d_dirs), int(d_pixels), int(d_count),
+                                    int(stream) or None))
+
     KERNELS = ("primary_rays", "shadow_setup", "shadow_rays", "shade_pixels")
 
     def set_timing(self, enable=True):
@@ -279,7 +287,7 @@ class VoxelRaytracer3D:
     def frame_times(self):
         """Device ms of the last frame's launches, in KERNELS order (waits for the frame)."""
         ms = (C.c_float * 4)()
-        _check(lib().vx_tracer_frame_times(self.h, ms))
+        _check(lib().vx_tracer_frame_times(self.h, C.byref(ms)))
         return [float(v) for v in ms]
 
     def render_host(self, cam, env, opts, W, H, bgra=None):

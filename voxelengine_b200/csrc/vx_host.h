@@ -98,5 +98,6 @@ struct vx_tracer {
     void* d_queue_rec = nullptr; void* d_queue_aux = nullptr; void* d_queue_lanes = nullptr;   // shadow queue of vx_render (one frame in flight per tracer)
     unsigned long long queue_cap = 0; size_t queue_aux_words = 0;
     int sm_count = 0;
+    bool primary_only = false; unsigned long long* last_queue_count = nullptr; // vx_bounce_rays reuses vx_render's primary pass
     bool timing = false; int timed_kernels = 0; cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // vx_tracer_set_timing
 };

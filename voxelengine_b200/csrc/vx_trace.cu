@@ -336,6 +336,46 @@ __global__ void __launch_bounds__(256) shade_pixels(FrameParams f, uint8_t* __re
     }
 }
 
+// Incoherent secondary rays (BASELINE config 5): the ambient-occlusion sample loop of Renderer.cu:121-165, sample i = 0.
+// One thread per queued primary hit; ray order follows the queue, `pixels` says which pixel each ray belongs to.
+__device__ __forceinline__ uint32_t noise_hash(uint32_t seed) { // cuda_noise.cuh:44-54
+    seed = (seed + 0x7ed55d16u) + (seed << 12);
+    seed = (seed ^ 0xc761c23cu) ^ (seed >> 19);
+    seed = (seed + 0x165667b1u) + (seed << 5);
+    seed = (seed + 0xd3a2646cu) ^ (seed << 9);
+    seed = (seed + 0xfd7046c5u) + (seed << 3);
+    seed = (seed ^ 0xb55a4f09u) ^ (seed >> 16);
+    return seed;
+}
+__device__ __forceinline__ float random_float(uint32_t seed) { return fdiv((float)noise_hash(seed), (float)0xffffffffu); } // :66-71
+
+template <int NORM>
+__global__ void __launch_bounds__(256) bounce_setup(FrameParams f, ShadowQueue q, float* __restrict__ origins, float* __restrict__ dirs,
+                                                    uint32_t* __restrict__ pixels) {
+    const unsigned long long n = *q.count;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const float4 r = q.rec[i];
+        const uint32_t pix = __float_as_uint(r.w);
+        const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
+        int ty = y; // thread coordinates: undo the checkerboard row mapping of Renderer.cu:186-194
+        if (f.checkerboard) ty = (y - ((x % 2) == 0 ? 1 : 0) - (f.frame_number % 2u == 0u ? 1 : 0)) / 2;
+        const V3 nn = normal_from_code(q.aux[i] >> 16);
+        const V3 n3 = mk(-nn.x, -nn.y, -nn.z); // the shading normal (screenDispatch negates what Raytrace returns)
+        const int seed = ty * (int)f.W + x;
+        const int si = seed + 0 * 1000 + ((int)f.frame_number + 1) * 1000;
+        V3 sd = mk(fsub(fmul(random_float((uint32_t)si), 2.0f), 1.0f), fsub(fmul(random_float((uint32_t)(si * 10)), 2.0f), 1.0f),
+                   fsub(fmul(random_float((uint32_t)(si * 100)), 2.0f), 1.0f));
+        sd = normalize3<NORM>(sd);
+        if (dot3(sd, n3) < 0.0f) { // reflect(i, n) = i - 2.0f * n * dot(n, i), helper_math.h:1427-1430
+            const float dn = dot3(n3, sd);
+            sd = mk(fsub(sd.x, fmul(fmul(2.0f, n3.x), dn)), fsub(sd.y, fmul(fmul(2.0f, n3.y), dn)), fsub(sd.z, fmul(fmul(2.0f, n3.z), dn)));
+        }
+        origins[3 * i] = fadd(r.x, fmul(n3.x, 0.01f)); origins[3 * i + 1] = fadd(r.y, fmul(n3.y, 0.01f)); origins[3 * i + 2] = fadd(r.z, fmul(n3.z, 0.01f));
+        dirs[3 * i] = sd.x; dirs[3 * i + 1] = sd.y; dirs[3 * i + 2] = sd.z;
+        pixels[i] = (uint32_t)y * f.W + (uint32_t)x;
+    }
+}
+
 template <int NORM, bool STATS>
 __global__ void __launch_bounds__(128, VX_MIN_BLOCKS) primary_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
                                                                    unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
@@ -598,6 +638,7 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
         if (rc) return rc;
         q.count = qc;
     }
+    t->last_queue_count = shadow_pass ? q.count : nullptr;
     unsigned long long *next1 = nullptr, *next2 = nullptr;
     rc = next_counter(t, cs, &next1);
     if (rc) return rc;
@@ -611,7 +652,7 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
         VX_MARK(0); \
         primary_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); \
         VX_MARK(1); t->timed_kernels = 1; \
-        if (shadow_pass) { \
+        if (shadow_pass && !t->primary_only) { \
             shadow_setup<N><<<dense_blocks, 256, 0, cs>>>(w, f, q); \
             VX_MARK(2); \
             rc = persistent_blocks(t, shadow_rays<N, S>, f.ids, blocks); if (rc) return rc; \
@@ -624,6 +665,40 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
 #undef VX_LAUNCH
 #undef VX_MARK
     VX_CUDA(cudaGetLastError());
+    return VX_OK;
+}
+
+extern "C" int vx_bounce_rays(vx_tracer* t, const vx_camera* cam, const vx_render_opts* opts, uint32_t W, uint32_t H, float* d_origins,
+                              float* d_dirs, uint32_t* d_pixels, unsigned long long* d_count, void* stream) {
+    VX_REQUIRE(t && cam && opts && d_origins && d_dirs && d_pixels && d_count, "NULL argument");
+    VX_REQUIRE(opts->norm_mode == VX_NORM_DEVICE || opts->norm_mode == VX_NORM_HOST, "bounce rays support VX_NORM_DEVICE or VX_NORM_HOST");
+    DeviceGuard guard(t->device);
+    cudaStream_t cs = (cudaStream_t)stream;
+    // the primary pass of a shadowed frame, into the tracer's own frame buffer; its hit queue is the input
+    const size_t bytes = (size_t)W * H * 4;
+    if (t->frame_bytes < bytes) {
+        VX_CUDA(cudaStreamSynchronize(cs));
+        cudaFree(t->d_frame); t->d_frame = nullptr; t->frame_bytes = 0;
+        VX_CUDA(cudaMalloc(&t->d_frame, bytes));
+        t->frame_bytes = bytes;
+    }
+    vx_render_opts o = *opts;
+    o.shadows = 1; o.debug_view = 0; o.d_stats = nullptr;
+    vx_env env = {{1.0f, 1.0f, 1.0f}, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}};
+    t->primary_only = true;
+    int rc = vx_render(t, cam, &env, &o, t->d_frame, nullptr, W, H, stream);
+    t->primary_only = false;
+    if (rc) return rc;
+    FrameParams f;
+    rc = fill_frame(t, cam, &env, &o, W, H, f);
+    if (rc) return rc;
+    if (!t->last_queue_count) { VX_CUDA(cudaMemsetAsync(d_count, 0, sizeof(unsigned long long), cs)); return VX_OK; }
+    ShadowQueue q{(float4*)t->d_queue_rec, (uint32_t*)t->d_queue_aux, (uint4*)t->d_queue_lanes, t->last_queue_count};
+    const unsigned dense_blocks = (unsigned)(t->sm_count > 0 ? t->sm_count : 148) * 8u;
+    if (o.norm_mode == VX_NORM_HOST) bounce_setup<1><<<dense_blocks, 256, 0, cs>>>(f, q, d_origins, d_dirs, d_pixels);
+    else bounce_setup<0><<<dense_blocks, 256, 0, cs>>>(f, q, d_origins, d_dirs, d_pixels);
+    VX_CUDA(cudaGetLastError());
+    VX_CUDA(cudaMemcpyAsync(d_count, t->last_queue_count, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, cs));
     return VX_OK;
 }
 
