@@ -7,6 +7,9 @@
 #include "vx_host.h"
 #include "vx_march.cuh"
 
+#ifndef VX_TRACE_MIN_BLOCKS
+#define VX_TRACE_MIN_BLOCKS 8 // same for the batch kernel (it carries the parity planes' counters too)
+#endif
 #ifndef VX_MIN_BLOCKS
 #define VX_MIN_BLOCKS 8 // resident 128-thread blocks per SM the render kernels are compiled for (register budget)
 #endif
@@ -69,7 +72,7 @@ struct BatchPolicy {
 };
 
 template <int NORM, bool COUNT>
-__global__ void __launch_bounds__(128) trace_rays(WorldView w, const float* __restrict__ origins, const float* __restrict__ dirs,
+__global__ void __launch_bounds__(128, VX_TRACE_MIN_BLOCKS) trace_rays(WorldView w, const float* __restrict__ origins, const float* __restrict__ dirs,
                                                   unsigned long long n, int max_steps, HitPlanes out, unsigned long long* next) {
     BatchPolicy<NORM, COUNT> pol;
     pol.origins = origins; pol.dirs = dirs; pol.n = n; pol.cap = max_steps; pol.out = out; pol.id = 0;
