@@ -241,8 +241,7 @@ __device__ __forceinline__ void fine_march8(const uint32_t* __restrict__ mask, V
         asm("{\n\t.reg .pred qz, qy, qx;\n\t.reg .f32 m, t;\n\t.reg .s32 c;\n\t"
             "min.f32 m, %0, %1;\n\t"
             "setp.le.f32 qz, %2, m;\n\t"
-            "setp.le.and.f32 qy, %1, %0, !qz;\n\t"
-            "setp.gt.and.f32 qx, %1, %0, !qz;\n\t"
+            "setp.le.and.f32 qy|qx, %1, %0, !qz;\n\t"
             "selp.f32 t, %1, %0, qy;\n\t"
             "selp.f32 t, %2, t, qz;\n\t"
             "selp.u32 %9, 1, 0, qy;\n\t"
@@ -388,8 +387,7 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
     asm("{\n\t.reg .pred pz, py, px;\n\t.reg .f32 m;\n\t"
         "min.f32 m, %0, %1;\n\t"
         "setp.le.f32 pz, %2, m;\n\t"
-        "setp.le.and.f32 py, %1, %0, !pz;\n\t"
-        "setp.gt.and.f32 px, %1, %0, !pz;\n\t"
+        "setp.le.and.f32 py|px, %1, %0, !pz;\n\t" // py = (ty <= tx) & !pz, px = !(ty <= tx) & !pz
         "@pz add.rn.f32 %2, %2, %6;\n\t"
         "@py add.rn.f32 %1, %1, %5;\n\t"
         "@px add.rn.f32 %0, %0, %4;\n\t"
@@ -424,6 +422,33 @@ constexpr int kFastQuad = 4;                // fast-loop steps between looks at 
 constexpr int kChunk = 32;                  // ray ids a warp draws at a time (render: one 8x4 pixel tile)
 constexpr int kFastChunk = VX_FAST_CHUNK;   // coarse steps a lane may take before the warp looks at the other states again
 
+// ST_FAST: the hot loop over the bordered linear grid; leaving the grid shows up as an occupied (border) cell.
+template <bool COUNT>
+__device__ __forceinline__ void lane_fast(const WorldView& w, Lane& L) {
+    const float dtx = lane_dt(L.d.x, L.ivx), dty = lane_dt(L.d.y, L.ivy), dtz = lane_dt(L.d.z, L.ivz);
+    const int dix = L.d.x > 0.0f ? 1 : -1, diy = L.d.y > 0.0f ? w.pnx : -w.pnx, diz = L.d.z > 0.0f ? w.pnxy : -w.pnxy;
+    float tx = L.tx, ty = L.ty, tz = L.tz;
+    uint32_t idx = L.idx;
+    int budget = kFastChunk;
+    // Lanes leave this loop one by one as they meet occupied cells.  Once most of the lanes that entered it are
+    // waiting, the few still stepping stop too (they stay ST_FAST and go on in the next round): a warp serves
+    // its majority.  Checked every kFastQuad steps; a scheduling heuristic only, results do not depend on it.
+    const int entered = __popc(__activemask());
+    bool found = false;
+#pragma unroll 1
+    do {
+#pragma unroll
+        for (int k = 0; k < kFastQuad; ++k) {
+            if (cell_bit(w.ptop, idx)) { found = true; break; }
+            if (COUNT) L.work.C++;
+            fast_step(tx, ty, tz, idx, dtx, dty, dtz, dix, diy, diz);
+        }
+        if (found) { lane_set_state(L, ST_CAND); break; }
+        budget -= kFastQuad;
+    } while (budget > 0 && __popc(__activemask()) * VX_LEAVE_DEN >= entered * VX_LEAVE_NUM);
+    L.tx = tx; L.ty = ty; L.tz = tz; L.idx = idx; L.bidx = idx;
+}
+
 template <bool BATCH, bool COUNT, class Policy>
 __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsigned long long* __restrict__ next) {
     const uint32_t lane = threadIdx.x & 31u;
@@ -441,35 +466,7 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
         V3 pos = mk(0.0f, 0.0f, 0.0f);
         uint32_t ncode = 0;
         if (lane_state(L) == ST_BEGIN) lane_begin(w, L, max_steps);
-        if (lane_state(L) == ST_FAST) {
-            // hot loop over the bordered linear grid: leaving the grid shows up as an occupied (border) cell
-            const float dtx = lane_dt(L.d.x, L.ivx), dty = lane_dt(L.d.y, L.ivy), dtz = lane_dt(L.d.z, L.ivz);
-            const int dix = L.d.x > 0.0f ? 1 : -1, diy = L.d.y > 0.0f ? w.pnx : -w.pnx, diz = L.d.z > 0.0f ? w.pnxy : -w.pnxy;
-            float tx = L.tx, ty = L.ty, tz = L.tz;
-            uint32_t idx = L.idx;
-            int budget = kFastChunk;
-            // Lanes leave this loop one by one as they meet occupied cells.  Once most of the lanes that entered it are
-            // waiting, the few still stepping stop too (they stay ST_FAST and go on in the next round): a warp serves
-            // its majority.  Checked every kFastQuad steps; a scheduling heuristic only, results do not depend on it.
-            const int entered = __popc(__activemask());
-            bool found = false;
-#pragma unroll 1
-            do {
-#pragma unroll
-                for (int k = 0; k < kFastQuad; ++k) {
-                    if (cell_bit(w.ptop, idx)) { found = true; break; }
-                    if (COUNT) L.work.C++;
-                    fast_step(tx, ty, tz, idx, dtx, dty, dtz, dix, diy, diz);
-                }
-                if (found) { lane_set_state(L, ST_CAND); break; }
-                budget -= kFastQuad;
-#ifdef VX_NOVOTE
-            } while (budget > 0);
-#else
-            } while (budget > 0 && __popc(__activemask()) * VX_LEAVE_DEN >= entered * VX_LEAVE_NUM);
-#endif
-            L.tx = tx; L.ty = ty; L.tz = tz; L.idx = idx; L.bidx = idx;
-        }
+        if (lane_state(L) == ST_FAST) lane_fast<COUNT>(w, L);
         if (lane_state(L) == ST_SLOW) lane_slow<COUNT>(w, L);
         if (lane_state(L) == ST_CAND) lane_cand<BATCH, COUNT>(w, L, pos, ncode);
         if (lane_state(L) == ST_DONE) pol.finish(w, L, pos, ncode);
