@@ -326,3 +326,22 @@ def test_bounce_rays_match_reference_sample_loop(vx, gpu_worlds, checkerboard, f
     ref8 = ow.trace(bo, bd, norm_mode=ol.NORM_HOST, max_steps=8)
     assert_same_hits(got8, ref8)
     rt.close()
+
+
+def test_render_host_sliced_path_equals_device_render(vx, gpu_worlds):
+    """vx_render_host renders large plain frames in slices to overlap the copy to the host; the bytes must be those of
+    one vx_render into device memory."""
+    import torch
+    dims, org = (128, 64, 128), (512, 0, 256)
+    w = gpu_worlds(dims, org, 8)
+    W, H = 320, 300  # >= 256 rows: sliced
+    cam = vx.make_camera((64, 90, 150), (-0.45, 0.3, 0.0), 90.0)
+    for dbg, sh in ((0, 1), (1, 0)):
+        rt = vx.VoxelRaytracer3D(w, 1)  # fresh device frame: pixels a mode does not write keep the caller's bytes
+        opts = vx.RenderOpts(0, 0, dbg, sh, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None)
+        frame = torch.full((H, W, 4), 7, dtype=torch.uint8, device="cuda")
+        rt.render_device(cam, vx.default_env(), opts, frame.data_ptr(), W, H)
+        torch.cuda.synchronize()
+        got = rt.render_host(cam, vx.default_env(), opts, W, H, bgra=np.full((H, W, 4), 7, np.uint8))
+        assert np.array_equal(got, frame.cpu().numpy())
+        rt.close()

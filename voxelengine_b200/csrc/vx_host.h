@@ -90,7 +90,7 @@ struct vx_tracer {
     int32_t* d_csteps = nullptr;
     int32_t* d_fsteps = nullptr;
     uint32_t* d_counters = nullptr;
-    void* d_frame = nullptr; size_t frame_bytes = 0; // vx_render_host
+    void* d_frame = nullptr; size_t frame_bytes = 0; bool frame_seeded = false; // vx_render_host
     float tan_arg = -1.0f, tan_val = 0.0f;           // cached device tanf
     cudaStream_t stream = nullptr;
     unsigned long long* d_next = nullptr;            // ring of ray counters for the persistent kernels
@@ -98,6 +98,7 @@ struct vx_tracer {
     void* d_queue_rec = nullptr; void* d_queue_aux = nullptr; void* d_queue_lanes = nullptr;   // shadow queue of vx_render (one frame in flight per tracer)
     unsigned long long queue_cap = 0; size_t queue_aux_words = 0;
     int sm_count = 0;
+    cudaStream_t copy_stream = nullptr; cudaEvent_t slice_ev[4] = {nullptr, nullptr, nullptr, nullptr}; // vx_render_host: copy/render overlap
     bool primary_only = false; unsigned long long* last_queue_count = nullptr; // vx_bounce_rays reuses vx_render's primary pass
     bool timing = false; int timed_kernels = 0; cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // vx_tracer_set_timing
 };

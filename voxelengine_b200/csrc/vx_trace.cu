@@ -6,6 +6,7 @@
 // ("policies") that feed it, the launches and the C ABI.
 #include "vx_host.h"
 #include "vx_march.cuh"
+#include <stdlib.h>
 
 #ifndef VX_TRACE_MIN_BLOCKS
 #define VX_TRACE_MIN_BLOCKS 8 // same for the batch kernel (it carries the parity planes' counters too)
@@ -434,6 +435,8 @@ extern "C" int vx_tracer_destroy(vx_tracer* t) {
     cudaFree(t->d_steps); cudaFree(t->d_voxel); cudaFree(t->d_brick); cudaFree(t->d_csteps); cudaFree(t->d_fsteps);
     cudaFree(t->d_counters); cudaFree(t->d_frame); cudaFree(t->d_next); cudaFree(t->d_queue_rec); cudaFree(t->d_queue_aux); cudaFree(t->d_queue_lanes);
     for (int i = 0; i < 5; ++i) if (t->ev[i]) cudaEventDestroy(t->ev[i]);
+    for (int i = 0; i < 4; ++i) if (t->slice_ev[i]) cudaEventDestroy(t->slice_ev[i]);
+    if (t->copy_stream) cudaStreamDestroy(t->copy_stream);
     if (t->stream) cudaStreamDestroy(t->stream);
     delete t;
     return VX_OK;
@@ -683,7 +686,7 @@ extern "C" int vx_bounce_rays(vx_tracer* t, const vx_camera* cam, const vx_rende
         VX_CUDA(cudaStreamSynchronize(cs));
         cudaFree(t->d_frame); t->d_frame = nullptr; t->frame_bytes = 0;
         VX_CUDA(cudaMalloc(&t->d_frame, bytes));
-        t->frame_bytes = bytes;
+        t->frame_bytes = bytes; t->frame_seeded = false;
     }
     vx_render_opts o = *opts;
     o.shadows = 1; o.debug_view = 0; o.d_stats = nullptr;
@@ -732,14 +735,45 @@ extern "C" int vx_render_host(vx_tracer* t, const vx_camera* cam, const vx_env* 
     if (t->frame_bytes < bytes) {
         cudaFree(t->d_frame); t->d_frame = nullptr; t->frame_bytes = 0;
         VX_CUDA(cudaMalloc(&t->d_frame, bytes));
-        t->frame_bytes = bytes;
+        t->frame_bytes = bytes; t->frame_seeded = false;
+    }
+    if (!t->frame_seeded) {
+        t->frame_seeded = true;
         // first use: seed the device frame with the caller's buffer so that unwritten pixels
         // (checkerboard, debug bottom-left) keep their previous value, as in the reference
         VX_CUDA(cudaMemcpyAsync(t->d_frame, h_bgra, bytes, cudaMemcpyHostToDevice, t->stream));
     }
-    int rc = vx_render(t, cam, env, opts, t->d_frame, nullptr, W, H, t->stream);
-    if (rc) return rc;
-    VX_CUDA(cudaMemcpyAsync(h_bgra, t->d_frame, bytes, cudaMemcpyDeviceToHost, t->stream));
+    // Large plain frames are rendered in horizontal slices so that the copy of one slice to the host overlaps the render of
+    // the next (second stream, one event per slice).  Two slices measured best at 4K (e2e 3975 -> 4060 Mrays/s; three and
+    // four lose more to launch tails than they hide, and letting the kernels store pixels straight into pinned host
+    // memory over PCIe is far slower: 2480 Mrays/s).  VX_HOST_SLICES=1..4 overrides.  Checkerboard frames (rows of neighbouring threads interleave) and
+    // callers that already partition the frame take the single-pass path.
+    static const uint32_t kSlices = [] { const char* e = getenv("VX_HOST_SLICES"); int v = e ? atoi(e) : 2; return (uint32_t)(v < 1 ? 1 : (v > 4 ? 4 : v)); }();
+    const bool sliced = opts && !opts->checkerboard && opts->tile_w == 0 && opts->tile_h == 0 && opts->band_count == 0 && kSlices > 1 && H >= 64u * kSlices;
+    if (!sliced) {
+        int rc = vx_render(t, cam, env, opts, t->d_frame, nullptr, W, H, t->stream);
+        if (rc) return rc;
+        VX_CUDA(cudaMemcpyAsync(h_bgra, t->d_frame, bytes, cudaMemcpyDeviceToHost, t->stream));
+        VX_CUDA(cudaStreamSynchronize(t->stream));
+        return VX_OK;
+    }
+    if (!t->copy_stream) {
+        VX_CUDA(cudaStreamCreateWithFlags(&t->copy_stream, cudaStreamNonBlocking));
+        for (uint32_t k = 0; k < kSlices; ++k) VX_CUDA(cudaEventCreateWithFlags(&t->slice_ev[k], cudaEventDisableTiming));
+    }
+    const uint32_t rows = ((H + kSlices - 1) / kSlices + 7u) / 8u * 8u;
+    for (uint32_t k = 0, y0 = 0; y0 < H; ++k, y0 += rows) {
+        vx_render_opts o = *opts;
+        o.tile_x0 = 0; o.tile_y0 = y0; o.tile_w = (W + 31u) / 32u * 32u; o.tile_h = rows;
+        int rc = vx_render(t, cam, env, &o, t->d_frame, nullptr, W, H, t->stream);
+        if (rc) return rc;
+        const uint32_t h = y0 + rows <= H ? rows : H - y0;
+        VX_CUDA(cudaEventRecord(t->slice_ev[k], t->stream));
+        VX_CUDA(cudaStreamWaitEvent(t->copy_stream, t->slice_ev[k], 0));
+        VX_CUDA(cudaMemcpyAsync((uint8_t*)h_bgra + (size_t)y0 * W * 4, (uint8_t*)t->d_frame + (size_t)y0 * W * 4, (size_t)h * W * 4,
+                                cudaMemcpyDeviceToHost, t->copy_stream));
+    }
+    VX_CUDA(cudaStreamSynchronize(t->copy_stream));
     VX_CUDA(cudaStreamSynchronize(t->stream));
     return VX_OK;
 }
