@@ -405,6 +405,7 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 //   void prepare(L)                       once per thread before any ray (e.g. a direction common to all rays)
 //   void init(w, id, L)                   set the lane up for ray `id` (lane_setup) or leave it ST_IDLE
 //   void finish(w, L, pos, ncode)         consume a finished march and set the lane ST_IDLE (or re-arm it)
+//   void flush()                          called by all 32 lanes whenever the whole warp is idle (before a refill / the end)
 //   kRefill                               idle lanes that trigger a refill (32: whole tiles only)
 // `next` is a zero-initialised device counter shared by all warps of the launch.
 // ---------------------------------------------------------------------------------------------
@@ -472,6 +473,7 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
         if (lane_state(L) == ST_DONE) pol.finish(w, L, pos, ncode);
         const uint32_t idle = __ballot_sync(kFull, lane_state(L) == ST_IDLE);
         if (idle) {
+            if (idle == kFull) pol.flush(); // the whole warp is between rays: results a policy holds back per tile go out now
             if (exhausted) { if (idle == kFull) break; continue; }
             if (__popc(idle) < Policy::kRefill) continue;
             if (cur == end) {

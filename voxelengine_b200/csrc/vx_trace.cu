@@ -36,6 +36,7 @@ struct BatchPolicy {
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return cap; }
     __device__ __forceinline__ void prepare(Lane&) {}
+    __device__ __forceinline__ void flush() {}
     __device__ __forceinline__ void init(const WorldView& w, unsigned long long i, Lane& L) {
         id = i;
         const float ff = (float)w.factor;
@@ -187,19 +188,44 @@ __device__ __forceinline__ void emit_pixel(const FrameParams& f, uint8_t* __rest
 
 template <int NORM, bool STATS>
 struct PrimaryPolicy {
-    static constexpr int kRefill = 32; // a warp takes a whole tile at a time: neighbouring rays stay in step
+    static constexpr int kRefill = 32; // a warp takes a whole tile at a time: neighbouring rays stay in step (2.2 ms instead of
+                                       // 1.56 ms per 4K frame with 16..28), and flush() relies on it
+#ifndef VX_SHADOW_REFILL
+#define VX_SHADOW_REFILL VX_REFILL_MIN
+#endif
     const FrameParams& f;
     uint8_t* __restrict__ bgra;
     int32_t* __restrict__ steps_plane;
     unsigned long long* __restrict__ stats;
     ShadowQueue q;
-    uint32_t pix; // per lane: x | y << 15 | crosshair thread << 30
+    uint32_t pix; // per lane: x | y << 15 | crosshair thread << 30 | hit staged << 31
+    float4* stage_rec; uint32_t* stage_aux; // shared memory, one slot per thread (x4 words with STATS)
 
     __device__ __forceinline__ PrimaryPolicy(const FrameParams& fp, uint8_t* b, int32_t* sp, unsigned long long* st, ShadowQueue sq)
         : f(fp), bgra(b), steps_plane(sp), stats(st), q(sq), pix(0) {}
     __device__ __forceinline__ unsigned long long count() const { return f.ids; }
     __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
     __device__ __forceinline__ void prepare(Lane&) {}
+    // The hits of a tile enter the frame's queue together and in pixel order, whenever the warp has finished the tile:
+    // the sun rays that shadow_rays later draws 32 at a time are then neighbours on the screen (coherent), which they are
+    // not if every lane appends the moment it finishes.
+    __device__ __forceinline__ void flush() {
+        const bool staged = pix >> 31;
+        const uint32_t m = __ballot_sync(kFull, staged);
+        if (!m) return;
+        const uint32_t lane = threadIdx.x & 31u;
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(q.count, (unsigned long long)__popc(m));
+        base = __shfl_sync(kFull, base, 0);
+        if (staged) {
+            const unsigned long long slot = base + (unsigned long long)__popc(m & ((1u << lane) - 1u));
+            const uint32_t tid = threadIdx.x;
+            q.rec[slot] = stage_rec[tid];
+            q.aux[slot] = stage_aux[tid];
+            if (STATS) { q.aux[slot + 2 * f.ids] = stage_aux[tid + 128]; q.aux[slot + 3 * f.ids] = stage_aux[tid + 256]; q.aux[slot + 4 * f.ids] = stage_aux[tid + 384]; }
+            pix &= 0x7FFFFFFFu;
+        }
+    }
 
     // getRayDirection, Renderer.cu:44-59
     __device__ __forceinline__ V3 primary_dir(int x, int y) const {
@@ -235,18 +261,12 @@ struct PrimaryPolicy {
         const bool hit = L.flags & F_HIT;
         const bool queued = hit && !f.debug_view && f.shadows; // the shadow Raytrace of Renderer.cu:102 runs in shadow_rays
         if (STATS) add_stats(stats, 1u, hit, 0u, 0u, queued ? 0u : (uint32_t)L.total, queued ? Work{0u, 0u, 0u} : L.work);
-        if (queued) {
-            const uint32_t m = __activemask();
-            const uint32_t lane = threadIdx.x & 31u, leader = (uint32_t)__ffs((int)m) - 1u;
-            unsigned long long base = 0;
-            if (lane == leader) base = atomicAdd(q.count, (unsigned long long)__popc(m));
-            base = __shfl_sync(m, base, (int)leader);
-            const unsigned long long slot = base + (unsigned long long)__popc(m & ((1u << lane) - 1u));
-            q.rec[slot] = make_float4(pos.x, pos.y, pos.z, __uint_as_float(pix));
-            q.aux[slot] = (uint32_t)L.total | (ncode << 16);
-            if (STATS) { // the primary's steps and work are added when its pixel is finished
-                q.aux[slot + 2 * f.ids] = L.work.C; q.aux[slot + 3 * f.ids] = L.work.K; q.aux[slot + 4 * f.ids] = L.work.E;
-            }
+        if (queued) { // staged in shared memory until the tile is complete, see flush()
+            const uint32_t tid = threadIdx.x;
+            stage_rec[tid] = make_float4(pos.x, pos.y, pos.z, __uint_as_float(pix));
+            stage_aux[tid] = (uint32_t)L.total | (ncode << 16);
+            if (STATS) { stage_aux[tid + 128] = L.work.C; stage_aux[tid + 256] = L.work.K; stage_aux[tid + 384] = L.work.E; }
+            pix |= 0x80000000u;
         } else {
             const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
             emit_pixel<NORM>(f, bgra, steps_plane, pix, hit, pos, ncode, false, L.total, hit ? pos : primary_dir(x, y));
@@ -289,7 +309,7 @@ __global__ void __launch_bounds__(256) shadow_setup(WorldView w, FrameParams f, 
 
 template <int NORM, bool STATS>
 struct ShadowPolicy {
-    static constexpr int kRefill = VX_REFILL_MIN;
+    static constexpr int kRefill = VX_SHADOW_REFILL;
     const FrameParams& f;
     ShadowQueue q;
     unsigned long long n;
@@ -298,6 +318,7 @@ struct ShadowPolicy {
     __device__ __forceinline__ ShadowPolicy(const FrameParams& fp, ShadowQueue sq) : f(fp), q(sq), n(*sq.count), slot(0) {}
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
+    __device__ __forceinline__ void flush() {}
     __device__ __forceinline__ void prepare(Lane& L) { // direction and slab inverses are the same for every sun ray
         V3 once;
         L.d = sun_direction<NORM>(f, once);
@@ -383,7 +404,10 @@ __global__ void __launch_bounds__(256) bounce_setup(FrameParams f, ShadowQueue q
 template <int NORM, bool STATS>
 __global__ void __launch_bounds__(128, VX_MIN_BLOCKS) primary_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
                                                                    unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
+    __shared__ float4 stage_rec[128];
+    __shared__ uint32_t stage_aux[STATS ? 512 : 128];
     PrimaryPolicy<NORM, STATS> pol(f, bgra, steps_plane, stats, q);
+    pol.stage_rec = stage_rec; pol.stage_aux = stage_aux;
     run_lanes<false, STATS>(w, pol, next);
 }
 template <int NORM, bool STATS>
