@@ -210,8 +210,7 @@ __device__ __forceinline__ void fine_march(const uint32_t* __restrict__ mask, in
     o.steps = steps;
 }
 
-// The same march for the common case: 8^3 brick, start strictly inside [0,8)^3 on every axis that matters (no IsOnEdge
-// padding), no NaN among the tMax values.  Identical arithmetic; what changes is bookkeeping: one range test for the
+// The same march for the common case: 8^3 brick, no NaN among the tMax values.  Identical arithmetic; what changes is bookkeeping: one range test for the
 // three cell coordinates, the bit index formed directly, the axis chosen by min (ties z over y over x, which is the
 // reference's chain when nothing is NaN), crossing coordinates on the stepped axis taken from the cell faces.
 __device__ __forceinline__ void fine_march8(const uint32_t* __restrict__ mask, V3 s, const Ray& r, FineOut& o) {
@@ -220,6 +219,7 @@ __device__ __forceinline__ void fine_march8(const uint32_t* __restrict__ mask, V
     float tx = r.d.x != 0.0f ? fdiv(fsub((float)(cx + ox), s.x), r.d.x) : CUDART_INF_F;
     float ty = r.d.y != 0.0f ? fdiv(fsub((float)(cy + oy), s.y), r.d.y) : CUDART_INF_F;
     float tz = r.d.z != 0.0f ? fdiv(fsub((float)(cz + oz), s.z), r.d.z) : CUDART_INF_F;
+    const bool on_edge = cx == 8 || cy == 8 || cz == 8;
     V3 point = s;
     uint32_t axis = 3u; // axis of the last counted step (3: none yet)
     int steps = 0;
@@ -232,8 +232,15 @@ __device__ __forceinline__ void fine_march8(const uint32_t* __restrict__ mask, V
     // The exits are labels so that the outcome flags are set once, after the loop, instead of being carried through it.
 #pragma unroll 1
     for (;;) {
-        if ((cx | cy | cz) & ~7) goto out_of_brick;
-        if (cell_bit(mask, (uint32_t)(cx + (cy << 3) + (cz << 6)))) goto hit_voxel;
+        uint32_t bit = (uint32_t)(cx + (cy << 3) + (cz << 6));
+        if ((cx | cy | cz) & ~7) {
+            // outside the brick, unless the march started on its far face (IsOnEdge, :216-232): then a coordinate equal to 8 is
+            // inside on the axes the ray descends along, and the voxel looked up is the clamped one (:240-246)
+            if (!on_edge || (unsigned)cx >= (unsigned)(ox ? 8 : 9) || (unsigned)cy >= (unsigned)(oy ? 8 : 9) || (unsigned)cz >= (unsigned)(oz ? 8 : 9))
+                goto out_of_brick;
+            bit = (uint32_t)(min(cx, 7) + (min(cy, 7) << 3) + (min(cz, 7) << 6));
+        }
+        if (cell_bit(mask, bit)) goto hit_voxel;
         float px, py, pz;
         uint32_t ax;
         // One step: axis of the minimum tMax (ties z over y over x), crossing point = start + t * direction except on the
@@ -273,7 +280,7 @@ __device__ __forceinline__ void fine_march8(const uint32_t* __restrict__ mask, V
         axis = ax;
     }
 hit_voxel:
-    o.hit = true; o.oob = false; o.cell = (uint32_t)cx | ((uint32_t)cy << 10) | ((uint32_t)cz << 20);
+    o.hit = true; o.oob = false; o.cell = (uint32_t)min(cx, 7) | ((uint32_t)min(cy, 7) << 10) | ((uint32_t)min(cz, 7) << 20);
     goto done;
 out_of_brick:
     o.hit = false; o.oob = true; o.cell = 0;
@@ -340,9 +347,8 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
     FineOut q;
     const uint32_t* mask = w.pool + (size_t)rec.y * w.words_per_brick;
     if (w.factor == 8) {
-        // fast variant when nothing can be NaN and the start is not on the padded far face (cell == 8 on some axis)
-        const bool plain = (L.flags & F_CAPOK) && (int)local.x != 8 && (int)local.y != 8 && (int)local.z != 8;
-        if (plain) fine_march8(mask, local, r, q);
+        // the tight variant whenever nothing can be NaN (the generic one keeps the reference's comparison order for NaNs)
+        if (L.flags & F_CAPOK) fine_march8(mask, local, r, q);
         else fine_march<true>(mask, 8, local, r, q);
     } else fine_march<false>(mask, w.factor, local, r, q);
     L.total += q.steps; L.fsteps += q.steps;
