@@ -215,7 +215,7 @@ __device__ __forceinline__ void fine_march(const uint32_t* __restrict__ mask, in
 // reference's chain when nothing is NaN), crossing coordinates on the stepped axis taken from the cell faces.
 __device__ __forceinline__ void fine_march8(const uint32_t* __restrict__ mask, V3 s, const Ray& r, FineOut& o) {
     int cx = (int)s.x, cy = (int)s.y, cz = (int)s.z;
-    const int ox = r.sx > 0, oy = r.sy > 0, oz = r.sz > 0;
+    int ox = r.sx > 0, oy = r.sy > 0, oz = r.sz > 0;
     float tx = r.d.x != 0.0f ? fdiv(fsub((float)(cx + ox), s.x), r.d.x) : CUDART_INF_F;
     float ty = r.d.y != 0.0f ? fdiv(fsub((float)(cy + oy), s.y), r.d.y) : CUDART_INF_F;
     float tz = r.d.z != 0.0f ? fdiv(fsub((float)(cz + oz), s.z), r.d.z) : CUDART_INF_F;
@@ -227,7 +227,7 @@ __device__ __forceinline__ void fine_march8(const uint32_t* __restrict__ mask, V
     int sx = r.sx, sy = r.sy, sz = r.sz;
 #ifndef VX_FINE_NO_PIN
     // keep the loop invariants in registers: left alone, the compiler re-derives them from the direction in every round
-    asm volatile("" : "+f"(dtx), "+f"(dty), "+f"(dtz), "+r"(sx), "+r"(sy), "+r"(sz), "+l"(mask));
+    asm volatile("" : "+f"(dtx), "+f"(dty), "+f"(dtz), "+r"(sx), "+r"(sy), "+r"(sz), "+r"(ox), "+r"(oy), "+r"(oz), "+l"(mask));
 #endif
     // The exits are labels so that the outcome flags are set once, after the loop, instead of being carried through it.
 #pragma unroll 1
