@@ -205,6 +205,31 @@ def run_ours(args, wl, wl_name):
     def gather():
         part.gather(frame)
 
+    # N > 1: the frame is rendered in row chunks and each chunk's bands start their way to rank 0 while the next chunk
+    # renders (FramePartition.render_and_gather); kernel times are summed over the chunks
+    chunk_ms = [0.0, 0.0, 0.0, 0.0]
+    chunk_opts = {}
+    cols = (W + 31) // 32 * 32
+
+    def render_rows(y0, h):
+        o = chunk_opts.get((y0, h))
+        if o is None:
+            o = chunk_opts[(y0, h)] = vx.RenderOpts(0, 0, 0, 1, 1, vx.NORM_DEVICE, 0, y0, cols, h, None, band_count, band_index)
+        render(o)
+        if timing_chunks[0]:
+            for i, v in enumerate(rt.frame_times()):
+                chunk_ms[i] += v
+    timing_chunks = [False]
+
+    def frame_step():
+        if world_size == 1:
+            render(o_timed)
+        elif args.gather_chunks <= 1:
+            render(o_timed)
+            gather()
+        else:
+            part.render_and_gather(frame, render_rows, args.gather_chunks)
+
     # counters of exactly this frame (untimed counting variants of the kernels): first the primary rays alone
     # (shadows off), then the whole frame
     o_prim = opts(stats.data_ptr())
@@ -231,9 +256,7 @@ def run_ours(args, wl, wl_name):
     o_timed = opts(None)
     for _ in range(max(args.warmup, 3)):
         flush.fill_(1)
-        render(o_timed)
-        if world_size > 1:
-            gather()
+        frame_step()
     torch.cuda.synchronize()
 
     # ---- timed region: K steps, device time by CUDA events on the launching stream -------------
@@ -246,21 +269,28 @@ def run_ours(args, wl, wl_name):
     kern_ms = [0.0, 0.0, 0.0, 0.0]
     for _ in range(args.steps):
         flush.fill_(1)  # L2 flush between timed iterations (512 MiB > 126 MB L2)
-        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(2))
         e0.record()
-        render(o_timed)
-        e1.record()
-        if world_size > 1:
-            gather()
+        frame_step()
         e2.record()
         e2.synchronize()
-        k_ms += e0.elapsed_time(e1)
         step_ms += e0.elapsed_time(e2)
-        kern_ms = [a + b for a, b in zip(kern_ms, rt.frame_times())]
+        if world_size == 1 or args.gather_chunks <= 1:
+            kern_ms = [a + b for a, b in zip(kern_ms, rt.frame_times())]
     torch.cuda.synchronize()
     if world_size > 1:
         dist.barrier()
     wall = time.perf_counter() - wall0
+    if world_size > 1 and args.gather_chunks > 1:
+        # per-kernel times of the chunked frame: an untimed extra pass (reading the events waits for each chunk)
+        timing_chunks[0] = True
+        for _ in range(args.steps):
+            flush.fill_(1)
+            frame_step()
+        torch.cuda.synchronize()
+        timing_chunks[0] = False
+        kern_ms = list(chunk_ms)
+    k_ms = sum(kern_ms[:4])
     rt.set_timing(False)
     t = torch.tensor([step_ms, k_ms] + kern_ms, dtype=torch.float64, device="cuda")
     if world_size > 1:
@@ -281,8 +311,7 @@ def run_ours(args, wl, wl_name):
         if world_size == 1:
             vx._check(vx.lib().vx_render_host(rt.h, C.byref(cam), C.byref(env), C.byref(o_timed), host.data_ptr(), W, H))
         else:
-            render(o_timed)
-            gather()
+            frame_step()
             if rank == 0:
                 host.copy_(frame[: H * W * 4], non_blocking=True)
             torch.cuda.synchronize()
@@ -290,7 +319,8 @@ def run_ours(args, wl, wl_name):
         dist.barrier()
     e2e_s = time.perf_counter() - t0
     e2e_rays_s = rays * args.steps / e2e_s / 1e6
-    return dict(vx=vx, rank=rank, world_size=world_size, rays=rays, st=st, alg_bytes_rank=alg_bytes_rank, step_ms=step_ms_max,
+    chunks = len(part.row_chunks(args.gather_chunks)) if world_size > 1 and args.gather_chunks > 1 else 1
+    return dict(chunks=chunks, vx=vx, rank=rank, world_size=world_size, rays=rays, st=st, alg_bytes_rank=alg_bytes_rank, step_ms=step_ms_max,
                 k_ms=k_ms_max, kern_ms=kern_ms, alg_primary=alg_primary, alg_shadow=alg_shadow, wall=wall, clocks=clocks, e2e=e2e_rays_s, h2d=h2d, d2h=d2h, info=info, cam_pos=cam_pos, world=world,
                 rt=rt, dev=dev)
 
@@ -329,6 +359,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather-chunks", type=int, default=int(os.environ.get("VX_GATHER_CHUNKS", "3")),
+                    help="N > 1: row chunks of the frame whose gather overlaps the next chunk's render (1 = render, then gather)")
     args = ap.parse_args()
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
     wl_name = args.workload or ("w2-4k" if max(args.gpus, world_size) == 1 else "w2-8k")
@@ -370,12 +402,13 @@ def main():
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl_name + ": " + wl["desc"], "camera": res["cam_pos"], "euler": wl["euler"], "fov_deg": 90,
                    "rays_per_step": res["rays"], "primary_rays": int(st[0]), "shadow_rays": int(st[2]), "steps_per_ray": float(st[4]) / res["rays"],
-                   "parallelism": "image bands x%d, world replicated" % res["world_size"], "l2": "flushed between timed steps (512 MiB write)",
+                   "parallelism": "image bands x%d, world replicated" % res["world_size"],
+                   "frame_chunks": res["chunks"], "l2": "flushed between timed steps (512 MiB write)",
                    "world": {"occupied_bricks": int(res["info"].occupied_bricks), "bricks": int(res["info"].bricks),
                              "pool_mb": res["info"].bytes_pool / 1e6, "build_ms": res["info"].build_ms}},
         "clocks": res["clocks"],
         "e2e": {"value": res["e2e"], "unit": "Mrays/s", "h2d_bytes_per_step": res["h2d"], "d2h_bytes_per_step": res["d2h"]},
-        "gpu_launches": 4 * K,
+        "gpu_launches": 4 * K * res["chunks"],
         "kernels_ms": dict(kern, frame=ms_kernel),
         # the dominant kernel first; the sun-ray march, the other half of the frame, beside it
         "roofline": roof("primary_rays", res["alg_primary"], "4*C + 8*K + 64*E of the primary rays + 4 B per miss pixel + 20 B per queued hit (SURVEY.md 8d)"),

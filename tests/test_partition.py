@@ -41,6 +41,16 @@ def _worker(rank, world_size, port, W, H, out_path):
         part.gather(frame)
     if rank == 0:
         np.save(out_path, view.numpy())
+    # the pipelined variant: render callback per row chunk, asynchronous gathers
+    view.fill_(255)
+    mine = set(rows)
+
+    def render_rows(y0, h):
+        ys = [y for y in range(y0, y0 + h) if y in mine]
+        view[ys] = full[ys]
+    part.render_and_gather(frame, render_rows, n_chunks=3)
+    if rank == 0:
+        np.save(out_path + ".pipelined.npy", view.numpy())
     dist.barrier()
     dist.destroy_process_group()
 
@@ -50,6 +60,7 @@ def test_band_gather_over_gloo(tmp_path, W, H, world_size):
     out = str(tmp_path / "frame.npy")
     mp.spawn(_worker, args=(world_size, _free_port(), W, H, out), nprocs=world_size, join=True)
     assert np.array_equal(np.load(out), _pattern(W, H))
+    assert np.array_equal(np.load(out + ".pipelined.npy"), _pattern(W, H))
 
 
 def test_band_ownership_covers_every_row_once():
@@ -64,6 +75,10 @@ def test_band_ownership_covers_every_row_once():
             assert p.render_opts() == (n, r)
         assert (seen == 1).all()
         assert FramePartition(W, H, 1, 0).render_opts() == (0, 0)
+        for k in (1, 2, 4, 7):
+            ch = p.row_chunks(k)
+            assert ch[0][0] == 0 and sum(h for _, h in ch) == H and len(ch) <= max(k, 1)
+            assert all(y0 % (BAND_ROWS * n) == 0 for y0, _ in ch)
         assert p.frame_bytes() == ((H + BAND_ROWS - 1) // BAND_ROWS) * BAND_ROWS * W * 4
 
 

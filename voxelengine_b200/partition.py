@@ -43,6 +43,51 @@ class FramePartition:
         """(band_count, band_index) for vx_render_opts; (0, 0) renders the whole frame."""
         return (self.world_size, self.rank) if self.world_size > 1 else (0, 0)
 
+    def row_chunks(self, n_chunks):
+        """Split the frame's rows into up to n_chunks ranges (y0, rows), each a whole number of band rounds
+        (BAND_ROWS * world_size rows) so that inside every chunk the bands are still dealt rank, rank + N, ..."""
+        rnd = BAND_ROWS * self.world_size
+        rounds = (self.H + rnd - 1) // rnd
+        per = max(1, (rounds + n_chunks - 1) // max(n_chunks, 1))
+        out, y = [], 0
+        while y < self.H:
+            h = min(per * rnd, self.H - y)
+            out.append((y, h))
+            y += per * rnd
+        return out
+
+    def render_and_gather(self, frame, render_rows, n_chunks=4, group=None):
+        """Pipelined frame: for every row chunk call render_rows(y0, rows) (which must enqueue this rank's render of
+        those rows on the current stream / do it synchronously on CPU), then start the gather of that chunk's bands
+        asynchronously, so the transfer of one chunk overlaps the render of the next.  Collective."""
+        if self.world_size == 1:
+            render_rows(0, self.H)
+            return frame
+        fb = self._views(frame)
+        chunks = self.row_chunks(n_chunks)
+        if self._send is None or self._send.device != frame.device:
+            self._send = torch.zeros(self.per_rank, self.band_bytes, dtype=torch.uint8, device=frame.device)
+            self._recv = ([torch.zeros_like(self._send) for _ in range(self.world_size)] if self.rank == 0 else None)
+        pending = []
+        for (y0, h) in chunks:
+            render_rows(y0, h)
+            b0, b1 = y0 // BAND_ROWS, (y0 + h + BAND_ROWS - 1) // BAND_ROWS          # global bands of the chunk
+            s0, s1 = b0 // self.world_size, (b1 + self.world_size - 1) // self.world_size  # their slots in the compact buffers
+            mine = fb[b0:b1][self.rank::self.world_size]                             # b0 is a multiple of world_size
+            n = mine.shape[0]
+            send = self._send[s0:s0 + max(s1 - s0, 1)]
+            send[:n].copy_(mine)
+            recv = [r[s0:s0 + send.shape[0]] for r in self._recv] if self.rank == 0 else None
+            work = dist.gather(send, recv, dst=0, group=group, async_op=True)
+            pending.append((work, b0, b1, recv))
+        for work, b0, b1, recv in pending:
+            work.wait()
+            if self.rank == 0:
+                for r in range(1, self.world_size):
+                    dst = fb[b0:b1][r::self.world_size]
+                    dst.copy_(recv[r][: dst.shape[0]])
+        return frame
+
     # ---- gather ------------------------------------------------------------------------------------
     def _views(self, frame):
         return frame.view(self.bands, self.band_bytes)
