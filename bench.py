@@ -8,7 +8,8 @@ every primary hit, the sun shadow ray and shading (BASELINE.json configs[2]/[3])
 
 N = 1   : 8192x512x8192 noise world, 8^3 bricks, 3840x2160, camera "overview" (SURVEY.md §8d config 3a).
 N > 1   : same world replicated on every GPU, 7680x4320 frame split into 8-row bands dealt round-robin
-          across ranks, framebuffer gathered to rank 0 with NCCL (config 4): strong scaling of one frame.
+          across ranks; rank 0 owns the frame and the other ranks' kernels store their pixels into it over NVLink
+          peer memory, closed by a fence (config 4; --exchange gather: NCCL gather instead): strong scaling of one frame.
 --impl reference : the CPU restatement of the reference's path (oracle/, kind "port": the reference has no
           CPU implementation of the 3-D march and its GPU build lives in oracle/_ref for parity only) on all
           host cores, each step a bounded row sample of the same frame.
@@ -34,7 +35,7 @@ WORKLOADS = {
                   desc="8192x512x8192 noise brickmap (8^3 bricks), 3840x2160 primary + sun-shadow rays, overview camera"),
     "w2-8k": dict(dims=(8192, 512, 8192), W=7680, H=4320, xz=(4096, 7936), lift=128, euler=(-0.5, 0.0, 0.0),
                   desc="8192x512x8192 noise brickmap (8^3 bricks), 7680x4320 primary + sun-shadow rays, 8-row bands "
-                       "round-robin over ranks, NCCL gather to rank 0"),
+                       "round-robin over ranks, frame assembled on rank 0"),
     "w1-1080p": dict(dims=(1024, 256, 1024), W=1920, H=1080, xz=(512, 960), lift=0, euler=(-0.45, 0.0, 0.0),
                      desc="1024x256x1024 noise brickmap (8^3 bricks), 1920x1080 primary + sun-shadow rays"),
 }
@@ -185,12 +186,18 @@ def run_ours(args, wl, wl_name):
     world = vx.World.from_noise(X, Y, Z, FACTOR, device=dev)
     info = world.info
     rt = vx.VoxelRaytracer3D(world, 16)
+    if "VX_FUSED_SHADE" in os.environ:  # experiments only; the default picks by where the frame lives
+        rt.set_fused_shade(int(os.environ["VX_FUSED_SHADE"]))
     cam, cam_pos = camera_for(vx, rt, wl)
     env = vx.default_env()
     stream = torch.cuda.current_stream().cuda_stream
-    from voxelengine_b200.partition import FramePartition
+    from voxelengine_b200.partition import FramePartition, SharedFrame
     part = FramePartition(W, H, world_size, rank)   # 8-row bands dealt round-robin over the ranks
-    frame = part.alloc_frame("cuda")
+    shared = SharedFrame(part, dev) if world_size > 1 and args.exchange == "shared" else None
+    frame = part.alloc_frame("cuda") if shared is None else None
+    if shared is not None and "VX_FUSED_SHADE" not in os.environ:
+        shared.attach(rt)
+    frame_ptr = shared.ptr if shared else frame.data_ptr()
     stats = torch.zeros(8, dtype=torch.int64, device="cuda")
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
     host = torch.empty(H * W * 4, dtype=torch.uint8).pin_memory() if rank == 0 else None
@@ -200,7 +207,7 @@ def run_ours(args, wl, wl_name):
         return vx.RenderOpts(0, 0, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, stats_ptr, band_count, band_index)
 
     def render(o):
-        rt.render_device(cam, env, o, frame.data_ptr(), W, H, stream=stream)
+        rt.render_device(cam, env, o, frame_ptr, W, H, stream=stream)
 
     def gather():
         part.gather(frame)
@@ -224,6 +231,10 @@ def run_ours(args, wl, wl_name):
     def frame_step():
         if world_size == 1:
             render(o_timed)
+        elif shared is not None:
+            # every rank's kernels store their pixels into rank 0's frame over NVLink; the fence is the only collective
+            render(o_timed)
+            shared.fence()
         elif args.gather_chunks <= 1:
             render(o_timed)
             gather()
@@ -275,13 +286,13 @@ def run_ours(args, wl, wl_name):
         e2.record()
         e2.synchronize()
         step_ms += e0.elapsed_time(e2)
-        if world_size == 1 or args.gather_chunks <= 1:
+        if world_size == 1 or shared is not None or args.gather_chunks <= 1:
             kern_ms = [a + b for a, b in zip(kern_ms, rt.frame_times())]
     torch.cuda.synchronize()
     if world_size > 1:
         dist.barrier()
     wall = time.perf_counter() - wall0
-    if world_size > 1 and args.gather_chunks > 1:
+    if world_size > 1 and shared is None and args.gather_chunks > 1:
         # per-kernel times of the chunked frame: an untimed extra pass (reading the events waits for each chunk)
         timing_chunks[0] = True
         for _ in range(args.steps):
@@ -313,14 +324,20 @@ def run_ours(args, wl, wl_name):
         else:
             frame_step()
             if rank == 0:
-                host.copy_(frame[: H * W * 4], non_blocking=True)
+                if shared is not None:
+                    shared.to_host(host, H * W * 4, stream)
+                else:
+                    host.copy_(frame[: H * W * 4], non_blocking=True)
             torch.cuda.synchronize()
     if world_size > 1:
         dist.barrier()
     e2e_s = time.perf_counter() - t0
     e2e_rays_s = rays * args.steps / e2e_s / 1e6
-    chunks = len(part.row_chunks(args.gather_chunks)) if world_size > 1 and args.gather_chunks > 1 else 1
-    return dict(chunks=chunks, vx=vx, rank=rank, world_size=world_size, rays=rays, st=st, alg_bytes_rank=alg_bytes_rank, step_ms=step_ms_max,
+    chunks = len(part.row_chunks(args.gather_chunks)) if world_size > 1 and shared is None and args.gather_chunks > 1 else 1
+    exchange = "none" if world_size == 1 else ("peer stores into rank 0's frame (CUDA IPC over NVLink) + fence" if shared else "torch.distributed gather to rank 0")
+    if shared is not None:
+        shared.close()
+    return dict(chunks=chunks, exchange=exchange, vx=vx, rank=rank, world_size=world_size, rays=rays, st=st, alg_bytes_rank=alg_bytes_rank, step_ms=step_ms_max,
                 k_ms=k_ms_max, kern_ms=kern_ms, alg_primary=alg_primary, alg_shadow=alg_shadow, wall=wall, clocks=clocks, e2e=e2e_rays_s, h2d=h2d, d2h=d2h, info=info, cam_pos=cam_pos, world=world,
                 rt=rt, dev=dev)
 
@@ -359,7 +376,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--gather-chunks", type=int, default=int(os.environ.get("VX_GATHER_CHUNKS", "3")),
+    ap.add_argument("--exchange", default=os.environ.get("VX_EXCHANGE", "shared"), choices=["shared", "gather"],
+                    help="N > 1: how the bands reach rank 0 (shared: peer stores into rank 0's frame; gather: NCCL gather)")
+    ap.add_argument("--gather-chunks", type=int, default=int(os.environ.get("VX_GATHER_CHUNKS", "1")),
                     help="N > 1: row chunks of the frame whose gather overlaps the next chunk's render (1 = render, then gather)")
     args = ap.parse_args()
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
@@ -403,7 +422,7 @@ def main():
         "config": {"workload": wl_name + ": " + wl["desc"], "camera": res["cam_pos"], "euler": wl["euler"], "fov_deg": 90,
                    "rays_per_step": res["rays"], "primary_rays": int(st[0]), "shadow_rays": int(st[2]), "steps_per_ray": float(st[4]) / res["rays"],
                    "parallelism": "image bands x%d, world replicated" % res["world_size"],
-                   "frame_chunks": res["chunks"], "l2": "flushed between timed steps (512 MiB write)",
+                   "frame_chunks": res["chunks"], "exchange": res["exchange"], "l2": "flushed between timed steps (512 MiB write)",
                    "world": {"occupied_bricks": int(res["info"].occupied_bricks), "bricks": int(res["info"].bricks),
                              "pool_mb": res["info"].bytes_pool / 1e6, "build_ms": res["info"].build_ms}},
         "clocks": res["clocks"],

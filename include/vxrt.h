@@ -177,7 +177,25 @@ int vx_bounce_rays(vx_tracer* t, const vx_camera* cam, const vx_render_opts* opt
  * events around them; vx_tracer_frame_times waits for the last frame and returns the four durations in ms (0 for
  * launches the frame did not need). */
 int vx_tracer_set_timing(vx_tracer* t, int enable);
+/* Where the hit pixels are shaded: 0 (default) = in the dense shade_pixels pass after the sun-ray march, fastest when
+ * the frame is in this GPU's memory; 1 = inside the march, 32 finished sun rays at a time (no shade_pixels launch):
+ * the pixel stores are spread over the march, which is what a frame mapped from another GPU (vx_shared_open) wants —
+ * partition.SharedFrame.attach sets it for such ranks.  Same pixels either way. */
+int vx_tracer_set_fused_shade(vx_tracer* t, int mode);
 int vx_tracer_frame_times(vx_tracer* t, float ms[4]);
+
+/* Shared frame for the multi-GPU frame partition (no reference counterpart: main.cu:95-99 has one cudaMalloc'd
+ * framebuffer on one GPU).  Rank 0 calls vx_shared_alloc and hands the 64-byte handle to the other ranks' processes,
+ * which vx_shared_open it (CUDA IPC, peer access over NVLink / NVSwitch) and pass the mapped pointer as vx_render's
+ * d_bgra together with their band_count / band_index: their kernels' pixel stores land in rank 0's HBM, and the only
+ * exchange left is a completion barrier.  vx_device_to_host copies from any device pointer (e.g. that frame) and
+ * waits for the copy. */
+#define VX_SHARED_HANDLE_BYTES 64
+int vx_shared_alloc(size_t bytes, int device, void** d_ptr, uint8_t handle[VX_SHARED_HANDLE_BYTES]);
+int vx_shared_open(const uint8_t handle[VX_SHARED_HANDLE_BYTES], int device, void** d_ptr);
+int vx_shared_close(void* d_ptr, int device); /* a pointer from vx_shared_open */
+int vx_shared_free(void* d_ptr, int device);  /* a pointer from vx_shared_alloc */
+int vx_device_to_host(void* h_dst, const void* d_src, size_t bytes, int device, void* stream);
 
 /* Device math the parity harness shares with the CPU oracle. */
 int vx_device_tanf(float x, float* out, int device);

@@ -238,6 +238,25 @@ def test_bands_and_tiles_compose_the_full_frame(vx, gpu_worlds):
         tiles = [(x0, y0, 96, 40) for y0 in range(0, rows, 40) for x0 in range(0, 224, 96)]  # thread-space rectangles
         tiled = render(passes=[vx.RenderOpts(cb, 2, 0, 1, 1, vx.NORM_DEVICE, x0, y0, tw, th, None) for (x0, y0, tw, th) in tiles])
         assert np.array_equal(whole[0], tiled[0]) and np.array_equal(whole[1], tiled[1]), "tiles, checkerboard %d" % cb
+    # shading inside the sun-ray march (the variant chosen for a frame in another GPU's memory) writes the same frame
+    whole = render(passes=[vx.RenderOpts(0, 2, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None)])
+    for norm in (vx.NORM_DEVICE, vx.NORM_HOST):
+        rt.set_fused_shade(0)
+        dense = render(passes=[vx.RenderOpts(0, 2, 0, 1, 1, norm, 0, 0, 0, 0, None)])
+        rt.set_fused_shade(1)
+        fused = render(passes=[vx.RenderOpts(0, 2, 0, 1, 1, norm, 0, 0, 0, 0, None)])
+        assert np.array_equal(dense[0], fused[0]) and np.array_equal(dense[1], fused[1]), "fused shade, norm %d" % norm
+    rt.set_fused_shade(0)
+    with pytest.raises(vx.VxError):
+        rt.set_fused_shade(2)
+    # row chunks x bands, the passes FramePartition.render_and_gather issues on N ranks (bench.py, N > 1)
+    from voxelengine_b200.partition import FramePartition
+    whole = render(passes=[vx.RenderOpts(0, 2, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None)])
+    for n in (2, 3):
+        chunks = FramePartition(W, H, n, 0).row_chunks(3)
+        passes = [vx.RenderOpts(0, 2, 0, 1, 1, vx.NORM_DEVICE, 0, y0, 224, h, None, n, r) for (y0, h) in chunks for r in range(n)]
+        chunked = render(passes=passes)
+        assert np.array_equal(whole[0], chunked[0]) and np.array_equal(whole[1], chunked[1]), "chunks x bands x%d" % n
     rt.close()
 
 

@@ -65,7 +65,8 @@ ABI_SYMBOLS = [
     "vx_last_error", "vx_version", "vx_device_count", "vx_world_build_noise", "vx_world_build_noise_full",
     "vx_world_from_dense_bits", "vx_world_destroy", "vx_world_get_info", "vx_world_download", "vx_tracer_create",
     "vx_tracer_destroy", "vx_trace", "vx_trace_device", "vx_hits_postprocess", "vx_get_directions", "vx_render",
-    "vx_render_host", "vx_bounce_rays", "vx_tracer_set_timing", "vx_tracer_frame_times", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
+    "vx_render_host", "vx_bounce_rays", "vx_tracer_set_timing", "vx_tracer_set_fused_shade", "vx_tracer_frame_times", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
+    "vx_shared_alloc", "vx_shared_open", "vx_shared_close", "vx_shared_free", "vx_device_to_host",
 ]
 
 _lib = None
@@ -104,6 +105,12 @@ def lib():
     L.vx_device_tanf.argtypes = [C.c_float, C.POINTER(C.c_float), i32]
     L.vx_device_normalize.argtypes = [vp, vp, sz, i32]
     L.vx_measure_read_bandwidth.argtypes = [i32, sz, i32, C.POINTER(C.c_float)]
+    L.vx_tracer_set_fused_shade.argtypes = [vp, i32]
+    L.vx_shared_alloc.argtypes = [sz, i32, C.POINTER(vp), C.c_char_p]
+    L.vx_shared_open.argtypes = [C.c_char_p, i32, C.POINTER(vp)]
+    L.vx_shared_close.argtypes = [vp, i32]
+    L.vx_shared_free.argtypes = [vp, i32]
+    L.vx_device_to_host.argtypes = [vp, vp, sz, i32, vp]
     _lib = L
     return L
 
@@ -160,6 +167,37 @@ def measure_read_bandwidth(nbytes, reps=20, device=0):
     out = C.c_float(0)
     _check(lib().vx_measure_read_bandwidth(device, int(nbytes), int(reps), C.byref(out)))
     return out.value
+
+
+SHARED_HANDLE_BYTES = 64
+
+
+def shared_alloc(nbytes, device=0):
+    """(device pointer, 64-byte handle) of a zeroed buffer other processes of this node can map (vx_shared_alloc)."""
+    ptr, handle = C.c_void_p(), C.create_string_buffer(SHARED_HANDLE_BYTES)
+    _check(lib().vx_shared_alloc(int(nbytes), device, C.byref(ptr), handle))
+    return ptr.value, handle.raw
+
+
+def shared_open(handle, device=0):
+    """Map another process's vx_shared_alloc buffer; the pointer is valid in this process's kernels (peer memory)."""
+    if len(handle) != SHARED_HANDLE_BYTES:
+        raise ValueError("handle must be %d bytes" % SHARED_HANDLE_BYTES)
+    ptr = C.c_void_p()
+    _check(lib().vx_shared_open(bytes(handle), device, C.byref(ptr)))
+    return ptr.value
+
+
+def shared_close(ptr, device=0):
+    _check(lib().vx_shared_close(ptr, device))
+
+
+def shared_free(ptr, device=0):
+    _check(lib().vx_shared_free(ptr, device))
+
+
+def device_to_host(host_ptr, dev_ptr, nbytes, device=0, stream=0):
+    _check(lib().vx_device_to_host(host_ptr, dev_ptr, int(nbytes), device, stream))
 
 
 def device_normalize(dirs, device=0):
@@ -283,6 +321,10 @@ class VoxelRaytracer3D:
     def set_timing(self, enable=True):
         """Record CUDA events around the launches of every following frame (vx_tracer_set_timing)."""
         _check(lib().vx_tracer_set_timing(self.h, 1 if enable else 0))
+
+    def set_fused_shade(self, mode):
+        """1: shade inside the sun-ray march (for a frame in another GPU's memory); 0: dense shade_pixels pass (default)."""
+        _check(lib().vx_tracer_set_fused_shade(self.h, int(mode)))
 
     def frame_times(self):
         """Device ms of the last frame's launches, in KERNELS order (waits for the frame)."""

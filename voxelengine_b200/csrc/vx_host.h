@@ -99,6 +99,7 @@ struct vx_tracer {
     unsigned long long queue_cap = 0; size_t queue_aux_words = 0;
     int sm_count = 0;
     cudaStream_t copy_stream = nullptr; cudaEvent_t slice_ev[4] = {nullptr, nullptr, nullptr, nullptr}; // vx_render_host: copy/render overlap
+    int fused_shade = 0;  // vx_tracer_set_fused_shade
     bool primary_only = false; unsigned long long* last_queue_count = nullptr; // vx_bounce_rays reuses vx_render's primary pass
     bool timing = false; int timed_kernels = 0; cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // vx_tracer_set_timing
 };

@@ -413,6 +413,8 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 //   void finish(w, L, pos, ncode)         consume a finished march and set the lane ST_IDLE (or re-arm it)
 //   void flush()                          called by all 32 lanes whenever the whole warp is idle (before a refill / the end)
 //   kRefill                               idle lanes that trigger a refill (32: whole tiles only)
+//   kDrain, void drain(uint32_t done)     kDrain: called by all 32 lanes once per round, after finish(), with the ballot of the
+//                                         lanes that finished this round (a policy batching its per-ray epilogue across the warp)
 // `next` is a zero-initialised device counter shared by all warps of the launch.
 // ---------------------------------------------------------------------------------------------
 #ifndef VX_REFILL_MIN
@@ -476,7 +478,13 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
         if (lane_state(L) == ST_FAST) lane_fast<COUNT>(w, L);
         if (lane_state(L) == ST_SLOW) lane_slow<COUNT>(w, L);
         if (lane_state(L) == ST_CAND) lane_cand<BATCH, COUNT>(w, L, pos, ncode);
-        if (lane_state(L) == ST_DONE) pol.finish(w, L, pos, ncode);
+        if constexpr (Policy::kDrain) {
+            const uint32_t done = __ballot_sync(kFull, lane_state(L) == ST_DONE);
+            if (lane_state(L) == ST_DONE) pol.finish(w, L, pos, ncode);
+            if (done) pol.drain(done);
+        } else {
+            if (lane_state(L) == ST_DONE) pol.finish(w, L, pos, ncode);
+        }
         const uint32_t idle = __ballot_sync(kFull, lane_state(L) == ST_IDLE);
         if (idle) {
             if (idle == kFull) pol.flush(); // the whole warp is between rays: results a policy holds back per tile go out now

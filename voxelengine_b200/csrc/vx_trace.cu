@@ -32,6 +32,7 @@ struct BatchPolicy {
     HitPlanes out;
     unsigned long long id; // per lane: the ray being marched
     static constexpr int kRefill = VX_REFILL_MIN;
+    static constexpr bool kDrain = false;
 
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return cap; }
@@ -188,6 +189,7 @@ __device__ __forceinline__ void emit_pixel(const FrameParams& f, uint8_t* __rest
 
 template <int NORM, bool STATS>
 struct PrimaryPolicy {
+    static constexpr bool kDrain = false;
     static constexpr int kRefill = 32; // a warp takes a whole tile at a time: neighbouring rays stay in step (2.2 ms instead of
                                        // 1.56 ms per 4K frame with 16..28), and flush() relies on it
 #ifndef VX_SHADOW_REFILL
@@ -307,18 +309,31 @@ __global__ void __launch_bounds__(256) shadow_setup(WorldView w, FrameParams f, 
     }
 }
 
-template <int NORM, bool STATS>
+//
+// FUSE: the march shades too, and shade_pixels is not launched.  A finished sun ray leaves (queue entry, result) in a
+// per-warp list in shared memory; whenever 32 are waiting the whole warp shades one each — the same dense work as
+// shade_pixels, but spread over the march.  For a frame that lives in another GPU's memory (the shared frame of the
+// multi-GPU partition, vx_shared_open) that spreads the pixel stores over the whole kernel instead of sending every
+// rank's pixels over NVLink in one burst at the end of the frame.
+constexpr uint32_t kShadeList = 64; // per warp: fewer than 32 waiting + at most 32 finishing in one round
+
+template <int NORM, bool STATS, bool FUSE>
 struct ShadowPolicy {
     static constexpr int kRefill = VX_SHADOW_REFILL;
+    static constexpr bool kDrain = FUSE;
     const FrameParams& f;
     ShadowQueue q;
+    uint8_t* __restrict__ bgra;
+    int32_t* __restrict__ steps_plane;
+    uint2* list;               // FUSE: this warp's kShadeList entries
     unsigned long long n;
     uint32_t slot;             // per lane: queue entry whose sun ray this lane marches
+    uint32_t head, waiting;    // FUSE, warp-uniform: the list is entries head .. head + waiting - 1 (mod kShadeList)
 
-    __device__ __forceinline__ ShadowPolicy(const FrameParams& fp, ShadowQueue sq) : f(fp), q(sq), n(*sq.count), slot(0) {}
+    __device__ __forceinline__ ShadowPolicy(const FrameParams& fp, ShadowQueue sq, uint8_t* b, int32_t* sp, uint2* l)
+        : f(fp), q(sq), bgra(b), steps_plane(sp), list(l), n(*sq.count), slot(0), head(0), waiting(0) {}
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
-    __device__ __forceinline__ void flush() {}
     __device__ __forceinline__ void prepare(Lane& L) { // direction and slab inverses are the same for every sun ray
         V3 once;
         L.d = sun_direction<NORM>(f, once);
@@ -336,9 +351,36 @@ struct ShadowPolicy {
     }
 
     __device__ __forceinline__ void finish(const WorldView&, Lane& L, V3, uint32_t) {
-        q.aux[slot + f.ids] = (uint32_t)L.total | ((L.flags & F_HIT) ? 0x80000000u : 0u);
-        if (STATS) { q.aux[slot + 5 * f.ids] = L.work.C; q.aux[slot + 6 * f.ids] = L.work.K; q.aux[slot + 7 * f.ids] = L.work.E; }
+        const uint32_t result = (uint32_t)L.total | ((L.flags & F_HIT) ? 0x80000000u : 0u);
+        if (FUSE) {
+            const uint32_t m = __activemask(), rank = (uint32_t)__popc(m & ((1u << (threadIdx.x & 31u)) - 1u));
+            list[(head + waiting + rank) & (kShadeList - 1u)] = make_uint2(slot, result);
+        } else {
+            q.aux[slot + f.ids] = result;
+            if (STATS) { q.aux[slot + 5 * f.ids] = L.work.C; q.aux[slot + 6 * f.ids] = L.work.K; q.aux[slot + 7 * f.ids] = L.work.E; }
+        }
         L.flags = ST_IDLE;
+    }
+
+    __device__ __forceinline__ void shade_waiting(uint32_t count) {
+        __syncwarp();
+        if ((threadIdx.x & 31u) < count) {
+            const uint2 e = list[(head + (threadIdx.x & 31u)) & (kShadeList - 1u)];
+            const float4 r = q.rec[e.x];
+            const uint32_t a = q.aux[e.x];
+            emit_pixel<NORM>(f, bgra, steps_plane, __float_as_uint(r.w), true, mk(r.x, r.y, r.z), a >> 16, (e.y >> 31) != 0u,
+                             (int)(a & 0xFFFFu) + (int)(e.y & 0x7FFFFFFFu), mk(0.0f, 0.0f, 0.0f));
+        }
+        __syncwarp();
+        head = (head + count) & (kShadeList - 1u);
+        waiting -= count;
+    }
+    __device__ __forceinline__ void drain(uint32_t done) { // all 32 lanes
+        waiting += (uint32_t)__popc(done);
+        if (waiting >= 32u) shade_waiting(32u);
+    }
+    __device__ __forceinline__ void flush() { // the whole warp is idle: whatever waits goes out (at the latest, at the end)
+        if (FUSE) { if (waiting >= 32u) shade_waiting(32u); if (waiting) shade_waiting(waiting); }
     }
 };
 
@@ -410,9 +452,11 @@ __global__ void __launch_bounds__(128, VX_MIN_BLOCKS) primary_rays(WorldView w, 
     pol.stage_rec = stage_rec; pol.stage_aux = stage_aux;
     run_lanes<false, STATS>(w, pol, next);
 }
-template <int NORM, bool STATS>
-__global__ void __launch_bounds__(128, VX_MIN_BLOCKS) shadow_rays(WorldView w, FrameParams f, ShadowQueue q, unsigned long long* next) {
-    ShadowPolicy<NORM, STATS> pol(f, q);
+template <int NORM, bool STATS, bool FUSE>
+__global__ void __launch_bounds__(128, VX_MIN_BLOCKS) shadow_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
+                                                                  ShadowQueue q, unsigned long long* next) {
+    __shared__ uint2 shade_list[FUSE ? 4 * kShadeList : 1];
+    ShadowPolicy<NORM, STATS, FUSE> pol(f, q, bgra, steps_plane, shade_list + (FUSE ? (threadIdx.x >> 5) * kShadeList : 0u));
     run_lanes<false, STATS>(w, pol, next);
 }
 
@@ -673,6 +717,7 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     rc = next_counter(t, cs, &next1);
     if (rc) return rc;
     if (shadow_pass) { rc = next_counter(t, cs, &next2); if (rc) return rc; }
+    const bool fuse = t->fused_shade != 0; // vx_tracer_set_fused_shade: a frame in another GPU's memory is shaded inside the march
     unsigned blocks = 1;
     const unsigned dense_blocks = (unsigned)(t->sm_count > 0 ? t->sm_count : 148) * 8u; // grid-stride over a device-side count
     // optional per-kernel timing (vx_tracer_set_timing): events between the launches, on the launching stream
@@ -685,10 +730,16 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
         if (shadow_pass && !t->primary_only) { \
             shadow_setup<N><<<dense_blocks, 256, 0, cs>>>(w, f, q); \
             VX_MARK(2); \
-            rc = persistent_blocks(t, shadow_rays<N, S>, f.ids, blocks); if (rc) return rc; \
-            shadow_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, q, next2); \
-            VX_MARK(3); \
-            shade_pixels<N, S><<<dense_blocks, 256, 0, cs>>>(f, (uint8_t*)d_bgra, d_steps, st, q); \
+            if (!S && fuse) { \
+                rc = persistent_blocks(t, shadow_rays<N, false, true>, f.ids, blocks); if (rc) return rc; \
+                shadow_rays<N, false, true><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, q, next2); \
+                VX_MARK(3); \
+            } else { \
+                rc = persistent_blocks(t, shadow_rays<N, S, false>, f.ids, blocks); if (rc) return rc; \
+                shadow_rays<N, S, false><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, q, next2); \
+                VX_MARK(3); \
+                shade_pixels<N, S><<<dense_blocks, 256, 0, cs>>>(f, (uint8_t*)d_bgra, d_steps, st, q); \
+            } \
             VX_MARK(4); t->timed_kernels = 4; } } while (0)
     if (opts->norm_mode == VX_NORM_HOST) { if (st) VX_LAUNCH(1, true); else VX_LAUNCH(1, false); }
     else { if (st) VX_LAUNCH(0, true); else VX_LAUNCH(0, false); }
@@ -729,6 +780,13 @@ extern "C" int vx_bounce_rays(vx_tracer* t, const vx_camera* cam, const vx_rende
     else bounce_setup<0><<<dense_blocks, 256, 0, cs>>>(f, q, d_origins, d_dirs, d_pixels);
     VX_CUDA(cudaGetLastError());
     VX_CUDA(cudaMemcpyAsync(d_count, t->last_queue_count, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, cs));
+    return VX_OK;
+}
+
+extern "C" int vx_tracer_set_fused_shade(vx_tracer* t, int mode) {
+    VX_REQUIRE(t != nullptr, "tracer is NULL");
+    VX_REQUIRE(mode == 0 || mode == 1, "mode is 0 or 1");
+    t->fused_shade = mode;
     return VX_OK;
 }
 

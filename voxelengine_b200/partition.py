@@ -4,6 +4,11 @@ bands are gathered to rank 0.  Rays never leave their GPU: the world is replicat
 
 Host-side only (torch tensors + torch.distributed); the same code runs over NCCL on CUDA tensors and over gloo on CPU
 tensors, which is how tests/test_partition.py covers it without a GPU.
+
+Two exchanges are offered.  SharedFrame (the default of bench.py on GPUs): rank 0 owns the frame, the other ranks map
+it over CUDA IPC and their frame kernels store pixels straight into rank 0's HBM over NVLink; the only collective left
+is a completion fence.  FramePartition.gather: every rank renders into its own frame and the bands travel in one
+torch.distributed gather (works on any backend).
 """
 import torch
 import torch.distributed as dist
@@ -108,3 +113,66 @@ class FramePartition:
                 dst = fb[r::self.world_size]
                 dst.copy_(self._recv[r][: dst.shape[0]])
         return frame
+
+
+class SharedFrame:
+    """The frame of a multi-GPU partition, living in rank 0's HBM and mapped by every other rank (vx_shared_alloc /
+    vx_shared_open, include/vxrt.h).  `ptr` is what each rank passes to render_device as d_bgra, with
+    FramePartition.render_opts() selecting its bands; after `fence()` rank 0's buffer holds the whole frame.
+
+    Collective constructor.  The handle travels through broadcast_object_list, so any backend does; every process must
+    have its CUDA device selected (`device` is the CUDA ordinal it renders on)."""
+
+    def __init__(self, part, device, group=None):
+        import voxelengine_b200 as vx
+        self._vx, self.part, self.device, self.group = vx, part, device, group
+        self.nbytes = part.frame_bytes()
+        self.owner = part.rank == 0
+        box = [None, None]
+        my_gpu = str(getattr(torch.cuda.get_device_properties(device), "uuid", device))
+        if self.owner:
+            self.ptr, handle = vx.shared_alloc(self.nbytes, device)
+            box = [handle, my_gpu]
+        if part.world_size > 1:
+            dist.broadcast_object_list(box, src=0, group=group)
+        if not self.owner:
+            self.ptr = vx.shared_open(box[0], device)
+        self.remote = box[1] != my_gpu   # the frame is in another GPU's memory: this rank's pixel stores cross NVLink
+        self._token = None
+
+    def attach(self, tracer):
+        """Tell a VoxelRaytracer3D of this rank where the frame lives: a rank writing into another GPU's memory shades
+        inside the sun-ray march (vx_tracer_set_fused_shade), which spreads its NVLink stores over the frame time."""
+        tracer.set_fused_shade(1 if self.remote else 0)
+
+    def fence(self):
+        """All ranks' pixel stores issued so far are in rank 0's buffer once this returns (NCCL: once the current
+        stream passes this point — the all-reduce is stream-ordered after each rank's kernels, and a kernel's peer
+        stores are performed before it completes)."""
+        if self.part.world_size == 1:
+            return
+        if dist.get_backend(self.group) == "nccl":
+            if self._token is None:
+                self._token = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", self.device))
+            dist.all_reduce(self._token, group=self.group)
+        else:
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=self.group)
+
+    def to_host(self, host, nbytes=None, stream=0):
+        """Rank 0: copy the first nbytes of the frame into a (pinned) host uint8 tensor and wait for it."""
+        self._vx.device_to_host(host.data_ptr(), self.ptr, self.nbytes if nbytes is None else nbytes, self.device, stream)
+
+    def close(self):
+        if self.ptr is None:
+            return
+        if self.part.world_size > 1:      # nobody unmaps or frees while another rank may still be writing
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=self.group)
+        if not self.owner:
+            self._vx.shared_close(self.ptr, self.device)
+        if self.part.world_size > 1:
+            dist.barrier(group=self.group)
+        if self.owner:
+            self._vx.shared_free(self.ptr, self.device)
+        self.ptr = None
