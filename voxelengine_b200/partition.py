@@ -142,8 +142,11 @@ class SharedFrame:
 
     def attach(self, tracer):
         """Tell a VoxelRaytracer3D of this rank where the frame lives: a rank writing into another GPU's memory shades
-        inside the sun-ray march (vx_tracer_set_fused_shade), which spreads its NVLink stores over the frame time."""
-        tracer.set_fused_shade(1 if self.remote else 0)
+        inside the sun-ray march (vx_tracer_set_fused_shade), which spreads its NVLink stores over the frame time
+        instead of all writers bursting into rank 0 together.  Measured on 8K frames (B200, NVSwitch): with 2 ranks the
+        dense pass is still faster (4.90 vs 5.00 ms), with 4 the fused one (2.63 vs 2.71 ms), with 8 clearly (1.46 vs
+        1.61 ms) — the burst costs about the same 0.2 ms however few pixels each writer has."""
+        tracer.set_fused_shade(1 if self.remote and self.part.world_size >= 4 else 0)
 
     def fence(self):
         """All ranks' pixel stores issued so far are in rank 0's buffer once this returns (NCCL: once the current
