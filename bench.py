@@ -200,7 +200,7 @@ def run_ours(args, wl, wl_name):
     frame_ptr = shared.ptr if shared else frame.data_ptr()
     stats = torch.zeros(8, dtype=torch.int64, device="cuda")
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
-    host = torch.empty(H * W * 4, dtype=torch.uint8).pin_memory() if rank == 0 else None
+    host = torch.empty(H * W * 4, dtype=torch.uint8).pin_memory() if world_size == 1 else None
     band_count, band_index = part.render_opts()
 
     def opts(stats_ptr=None):
@@ -310,11 +310,28 @@ def run_ours(args, wl, wl_name):
     kern_ms = [float(v) for v in t.cpu()[2:]]
     clocks = sampler.stop() if sampler else None
 
+    exchange = "none" if world_size == 1 else ("peer stores into rank 0's frame (CUDA IPC over NVLink) + fence" if shared else "torch.distributed gather to rank 0")
     # ---- e2e: the reference-facing call with HOST buffers (RenderScreen + cudaMemcpy of main.cu:165-167) ----
     e2e_rays_s = None
     d2h = W * H * 4
     h2d = C.sizeof(vx.Camera) + C.sizeof(vx.Env) + C.sizeof(vx.RenderOpts)
+    hostframe = None
     if world_size > 1:
+        # N > 1: one pinned host frame shared by the ranks' processes; every rank renders its bands into its own device
+        # frame and copies them down its own PCIe link (HostFrame) — the GPUs exchange nothing on this path
+        from voxelengine_b200.partition import HostFrame
+        if shared is not None:
+            shared.close()
+            shared = None
+        rt.set_fused_shade(0)
+        hostframe = HostFrame(part, dev)
+        local = frame if frame is not None else part.alloc_frame("cuda")
+
+        def e2e_step():
+            rt.render_device(cam, env, o_timed, local.data_ptr(), W, H, stream=stream)
+            hostframe.store(local.data_ptr(), stream)
+            hostframe.fence()
+        e2e_step()
         dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -322,21 +339,14 @@ def run_ours(args, wl, wl_name):
         if world_size == 1:
             vx._check(vx.lib().vx_render_host(rt.h, C.byref(cam), C.byref(env), C.byref(o_timed), host.data_ptr(), W, H))
         else:
-            frame_step()
-            if rank == 0:
-                if shared is not None:
-                    shared.to_host(host, H * W * 4, stream)
-                else:
-                    host.copy_(frame[: H * W * 4], non_blocking=True)
-            torch.cuda.synchronize()
+            e2e_step()
     if world_size > 1:
         dist.barrier()
     e2e_s = time.perf_counter() - t0
     e2e_rays_s = rays * args.steps / e2e_s / 1e6
+    if hostframe is not None:
+        hostframe.close()
     chunks = len(part.row_chunks(args.gather_chunks)) if world_size > 1 and shared is None and args.gather_chunks > 1 else 1
-    exchange = "none" if world_size == 1 else ("peer stores into rank 0's frame (CUDA IPC over NVLink) + fence" if shared else "torch.distributed gather to rank 0")
-    if shared is not None:
-        shared.close()
     return dict(chunks=chunks, exchange=exchange, vx=vx, rank=rank, world_size=world_size, rays=rays, st=st, alg_bytes_rank=alg_bytes_rank, step_ms=step_ms_max,
                 k_ms=k_ms_max, kern_ms=kern_ms, alg_primary=alg_primary, alg_shadow=alg_shadow, wall=wall, clocks=clocks, e2e=e2e_rays_s, h2d=h2d, d2h=d2h, info=info, cam_pos=cam_pos, world=world,
                 rt=rt, dev=dev)

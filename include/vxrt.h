@@ -196,6 +196,15 @@ int vx_shared_open(const uint8_t handle[VX_SHARED_HANDLE_BYTES], int device, voi
 int vx_shared_close(void* d_ptr, int device); /* a pointer from vx_shared_open */
 int vx_shared_free(void* d_ptr, int device);  /* a pointer from vx_shared_alloc */
 int vx_device_to_host(void* h_dst, const void* d_src, size_t bytes, int device, void* stream);
+/* The frame for a consumer on the host (main.cu:165-167 copies it down every frame) when several ranks render it: one
+ * host frame of W*H*4 bytes in memory all the ranks' processes map (POSIX shared memory), page-locked in each process
+ * by vx_host_register; after vx_render with band_count / band_index into its own device frame, each rank's
+ * vx_bands_to_host enqueues the copy of exactly its 8-row bands into their places of the host frame on `stream` —
+ * every rank down its own PCIe link, no GPU-to-GPU exchange.  The caller synchronises the streams and the ranks. */
+int vx_host_register(void* h_ptr, size_t bytes);
+int vx_host_unregister(void* h_ptr);
+int vx_bands_to_host(void* h_frame, const void* d_frame, uint32_t W, uint32_t H, uint32_t band_count, uint32_t band_index,
+                     int device, void* stream);
 
 /* Device math the parity harness shares with the CPU oracle. */
 int vx_device_tanf(float x, float* out, int device);

@@ -44,6 +44,18 @@ def _worker(rank, world_size, port, out_path):
         torch.cuda.synchronize()
         np.save(out_path, np.stack([host.numpy(), whole.cpu().numpy()]))
     sf.close()
+    # the same frame for a consumer on the host: every rank copies its own bands into one shared, pinned host frame
+    from voxelengine_b200.partition import HostFrame
+    hf = HostFrame(part, 0)
+    mine = torch.full((part.frame_bytes(),), 9, dtype=torch.uint8, device="cuda")
+    rt.set_fused_shade(0)
+    rt.render_device(cam, vx.default_env(), vx.RenderOpts(0, 1, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None, bc, bi), mine.data_ptr(), W, H)
+    hf.store(mine.data_ptr())
+    hf.fence()
+    if rank == 0:
+        np.save(out_path + ".host.npy", np.array(hf.array).reshape(-1))
+    hf.fence()
+    hf.close()
     rt.close()
     dist.destroy_process_group()
 
@@ -57,6 +69,7 @@ def test_ranks_render_into_rank0_frame(tmp_path, world_size):
     got, want = np.load(out)
     assert want.any()
     assert np.array_equal(got, want)
+    assert np.array_equal(np.load(out + ".host.npy"), want)  # H = 203: the last band is ragged
 
 
 def test_shared_handle_validation():

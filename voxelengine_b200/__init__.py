@@ -67,6 +67,7 @@ ABI_SYMBOLS = [
     "vx_tracer_destroy", "vx_trace", "vx_trace_device", "vx_hits_postprocess", "vx_get_directions", "vx_render",
     "vx_render_host", "vx_bounce_rays", "vx_tracer_set_timing", "vx_tracer_set_fused_shade", "vx_tracer_frame_times", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
     "vx_shared_alloc", "vx_shared_open", "vx_shared_close", "vx_shared_free", "vx_device_to_host",
+    "vx_host_register", "vx_host_unregister", "vx_bands_to_host",
 ]
 
 _lib = None
@@ -111,6 +112,9 @@ def lib():
     L.vx_shared_close.argtypes = [vp, i32]
     L.vx_shared_free.argtypes = [vp, i32]
     L.vx_device_to_host.argtypes = [vp, vp, sz, i32, vp]
+    L.vx_host_register.argtypes = [vp, sz]
+    L.vx_host_unregister.argtypes = [vp]
+    L.vx_bands_to_host.argtypes = [vp, vp, u32, u32, u32, u32, i32, vp]
     _lib = L
     return L
 
@@ -198,6 +202,19 @@ def shared_free(ptr, device=0):
 
 def device_to_host(host_ptr, dev_ptr, nbytes, device=0, stream=0):
     _check(lib().vx_device_to_host(host_ptr, dev_ptr, int(nbytes), device, stream))
+
+
+def host_register(ptr, nbytes):
+    _check(lib().vx_host_register(ptr, int(nbytes)))
+
+
+def host_unregister(ptr):
+    _check(lib().vx_host_unregister(ptr))
+
+
+def bands_to_host(host_ptr, dev_ptr, W, H, band_count=0, band_index=0, device=0, stream=0):
+    """Enqueue the copy of this rank's 8-row bands of a W x H BGRA frame from its device frame to the host frame."""
+    _check(lib().vx_bands_to_host(host_ptr, dev_ptr, W, H, band_count, band_index, device, stream))
 
 
 def device_normalize(dirs, device=0):

@@ -56,3 +56,43 @@ extern "C" int vx_device_to_host(void* h_dst, const void* d_src, size_t bytes, i
     VX_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return VX_OK;
 }
+
+// ---- the frame in host memory shared by the ranks' processes ---------------------------------------------------------
+// For a consumer on the host (main.cu:165-167 copies the frame down every frame) the bands need not meet on one GPU at
+// all: every rank copies the bands it rendered straight into one host frame (POSIX shared memory, pinned in each
+// process by vx_host_register), down its own PCIe link, all ranks at once.
+extern "C" int vx_host_register(void* h_ptr, size_t bytes) {
+    VX_REQUIRE(h_ptr && bytes, "NULL argument or empty buffer");
+    VX_CUDA(cudaHostRegister(h_ptr, bytes, cudaHostRegisterPortable));
+    return VX_OK;
+}
+
+extern "C" int vx_host_unregister(void* h_ptr) {
+    VX_REQUIRE(h_ptr != nullptr, "NULL argument");
+    VX_CUDA(cudaHostUnregister(h_ptr));
+    return VX_OK;
+}
+
+extern "C" int vx_bands_to_host(void* h_frame, const void* d_frame, uint32_t W, uint32_t H, uint32_t band_count, uint32_t band_index,
+                                int device, void* stream) {
+    VX_REQUIRE(h_frame && d_frame, "NULL argument");
+    VX_REQUIRE(W > 0 && H > 0, "empty frame");
+    if (band_count == 0) { band_count = 1; band_index = 0; }
+    VX_REQUIRE(band_index < band_count, "band_index must be below band_count");
+    DeviceGuard guard(device);
+    const size_t band_bytes = (size_t)W * 4u * 8u, row_bytes = (size_t)W * 4u;
+    const uint32_t bands = (H + 7u) / 8u;
+    if (band_index >= bands) return VX_OK;
+    const uint32_t mine = (bands - band_index + band_count - 1u) / band_count;
+    const uint32_t last = band_index + (mine - 1u) * band_count;                  // my last band may be cut by the frame's end
+    const bool ragged = (size_t)(last + 1u) * 8u > H;
+    const uint32_t full = ragged ? mine - 1u : mine;
+    const size_t off = (size_t)band_index * band_bytes, pitch = (size_t)band_count * band_bytes;
+    cudaStream_t cs = (cudaStream_t)stream;
+    if (full) VX_CUDA(cudaMemcpy2DAsync((char*)h_frame + off, pitch, (const char*)d_frame + off, pitch, band_bytes, full, cudaMemcpyDeviceToHost, cs));
+    if (ragged) {
+        const size_t o = (size_t)last * band_bytes;
+        VX_CUDA(cudaMemcpyAsync((char*)h_frame + o, (const char*)d_frame + o, ((size_t)H - (size_t)last * 8u) * row_bytes, cudaMemcpyDeviceToHost, cs));
+    }
+    return VX_OK;
+}

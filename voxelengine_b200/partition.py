@@ -179,3 +179,66 @@ class SharedFrame:
         if self.owner:
             self._vx.shared_free(self.ptr, self.device)
         self.ptr = None
+
+
+class HostFrame:
+    """The frame in host memory for a consumer on the CPU side (the reference copies its frame down every frame,
+    main.cu:165-167), shared by all ranks' processes: a file in /dev/shm that every rank maps and page-locks
+    (vx_host_register).  Each rank renders its bands into its own device frame and `store(d_frame_ptr)` copies exactly
+    those bands into place (vx_bands_to_host) — N PCIe links working at once and nothing crossing between the GPUs.
+    After `fence()` the host frame is whole; `array` is its numpy view (H x W x 4 bytes, B,G,R,A).
+
+    Collective constructor; any backend (the name travels through broadcast_object_list).  Single node only."""
+
+    def __init__(self, part, device, group=None):
+        import mmap
+        import os
+        import ctypes
+        import numpy as np
+        import voxelengine_b200 as vx
+        self._vx, self.part, self.device, self.group = vx, part, device, group
+        self.nbytes = part.frame_bytes()
+        box = [None]
+        if part.rank == 0:
+            box[0] = "/dev/shm/vxrt_frame_%d_%s" % (os.getpid(), os.urandom(4).hex())
+            fd = os.open(box[0], os.O_CREAT | os.O_EXCL | os.O_RDWR, 0o600)
+            os.ftruncate(fd, self.nbytes)
+        if part.world_size > 1:
+            dist.broadcast_object_list(box, src=0, group=group)
+        self.path = box[0]
+        if part.rank != 0:
+            fd = os.open(self.path, os.O_RDWR)
+        self._map = mmap.mmap(fd, self.nbytes)
+        os.close(fd)
+        self._view = (ctypes.c_uint8 * self.nbytes).from_buffer(self._map)
+        self.ptr = ctypes.addressof(self._view)
+        vx.host_register(self.ptr, self.nbytes)
+        self.array = np.frombuffer(self._map, np.uint8, part.H * part.W * 4).reshape(part.H, part.W, 4)
+        if part.world_size > 1:
+            dist.barrier(group=group)   # everyone has it mapped: the name can go
+        if part.rank == 0:
+            os.unlink(self.path)
+
+    def store(self, d_frame_ptr, stream=0):
+        """Enqueue the copy of this rank's bands from its device frame into the host frame (on `stream`)."""
+        bc, bi = self.part.render_opts()
+        self._vx.bands_to_host(self.ptr, d_frame_ptr, self.part.W, self.part.H, bc, bi, self.device, stream)
+
+    def fence(self):
+        """Every rank's copies enqueued so far have landed when this returns on every rank."""
+        torch.cuda.synchronize(self.device)
+        if self.part.world_size > 1:
+            dist.barrier(group=self.group)
+
+    def close(self):
+        if self._map is None:
+            return
+        torch.cuda.synchronize(self.device)
+        self._vx.host_unregister(self.ptr)
+        self.array = None
+        self._view = None
+        try:
+            self._map.close()
+        except BufferError:   # a caller still holds a view of `array`; the mapping goes with the last reference
+            pass
+        self._map = None
