@@ -176,6 +176,9 @@ inline void RenderScreen(VoxelRaytracer3D* rt, uint32_t screen_width, uint32_t s
     vx_camera cam{};
     memcpy(cam.origin, &origin, 12); memcpy(cam.fwd, &camera_fwd, 12); memcpy(cam.up, &camera_up, 12); memcpy(cam.right, &camera_right, 12);
     cam.fov_deg = s.fov;
+#ifdef ORTHO // the reference's compile-time switch (Renderer.cuh:13, Renderer.cu:202-204)
+    cam.ortho_w = s.ortho.x; cam.ortho_h = s.ortho.y;
+#endif
     vx_render_opts o{};
     o.checkerboard = s.checkerboard; o.frame_number = s.frame; o.debug_view = s.debug_view; o.shadows = s.shadows; o.crosshair = 1;
     o.norm_mode = VX_NORM_DEVICE;

@@ -133,6 +133,9 @@ typedef struct vx_camera {
     float origin[3], fwd[3], up[3], right[3]; /* as produced by Graphics::GetDirections */
     float fov_deg;                            /* SetFOV */
     float tan_half;                           /* 0: tanf(fov/2) evaluated on the device as the reference does */
+    float ortho_w, ortho_h;                   /* both > 0: the reference's ORTHO build (Renderer.cuh:13; getRayDirectionOrtho,
+                                                 Renderer.cu:61-70,202-204) with SetOrthoWindowSize(ortho_w, ortho_h): every ray
+                                                 runs along fwd, its origin moves across the window; 0: perspective */
 } vx_camera;
 typedef struct vx_env { float light_dir[3], light_color[3], ambient[3]; } vx_env; /* Renderer.cuh:33-37 */
 typedef struct vx_render_opts {

@@ -6,7 +6,8 @@
  * SDL and then one of:
  *   build  X Y Z factor out.bin                      dump GenerateLowresVoxelBuffer(CreateVoxels(..))
  *   trace  X Y Z factor rays.bin out.bin             VoxelRaytracer3D::Raytrace on rays.bin (n, origins, dirs)
- *   render X Y Z factor W H px py pz ex ey ez frames out.bgra   Graphics::RenderScreen, `frames` times
+ *   render X Y Z factor W H px py pz ex ey ez frames out.bgra [ow oh]   Graphics::RenderScreen, `frames` times
+ *                                                              (ow oh: SetOrthoWindowSize, used by the -DORTHO build)
  * Timings are printed as "key=value" lines.
  */
 #include "VolumeRaytracer.cuh"
@@ -108,7 +109,7 @@ int main(int argc, char** argv) {
         env.AmbientColor = make_float3(0.5f, 0.5f, 0.5f);
         SetEnvironment(env);
         SetFOV(90);
-        SetOrthoWindowSize(make_float2(10, 10));
+        SetOrthoWindowSize(argc >= 18 ? make_float2(atof(argv[16]), atof(argv[17])) : make_float2(10, 10));
         void* d_pixels = nullptr;
         cudaMalloc(&d_pixels, (size_t)W * H * 4);
         cudaMemset(d_pixels, 255, (size_t)W * H * 4); // main.cu:69

@@ -88,6 +88,7 @@ typedef struct vxo_camera {
     float origin[3], fwd[3], up[3], right[3];
     float fov_deg;
     float tan_half; /* > 0: use this value for tanf(fov/2) (e.g. the device's), else host tanf */
+    float ortho_w, ortho_h; /* both > 0: the ORTHO build (Renderer.cuh:13, Renderer.cu:61-70,202-204) with this OrthoSize */
 } vxo_camera;
 typedef struct vxo_env { float light_dir[3], light_color[3], ambient[3]; } vxo_env;
 typedef struct vxo_render_opts {

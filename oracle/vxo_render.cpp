@@ -76,6 +76,26 @@ V3 primary_dir(const Frame& f, int x, int y) {
     return norm3(d, f.o->norm_mode);
 }
 
+/* getRayDirectionOrtho, Renderer.cu:61-70: direction = fwd as given (Raytrace normalises it, once), the origin moves
+ * across the window: origin += right * (u*2-1) * size.x * ratio; origin += up * (v*2-1) * size.y — float3 * float
+ * products left to right, each a rounded float (helper_math operator*, operator+=) */
+bool ortho(const Frame& f) { return f.cam->ortho_w > 0.0f && f.cam->ortho_h > 0.0f; }
+V3 ortho_origin(const Frame& f, int x, int y) {
+    const float u0 = (float)x / (float)f.W, v0 = (float)y / (float)f.H;
+    const float ratio = (float)f.W / (float)f.H;
+    const float a = u0 * 2.0f - 1.0f, b = v0 * 2.0f - 1.0f;
+    const V3 U{f.cam->up[0], f.cam->up[1], f.cam->up[2]}, R{f.cam->right[0], f.cam->right[1], f.cam->right[2]};
+    V3 o{f.cam->origin[0], f.cam->origin[1], f.cam->origin[2]};
+    V3 t{R.x * a, R.y * a, R.z * a};
+    t = V3{t.x * f.cam->ortho_w, t.y * f.cam->ortho_w, t.z * f.cam->ortho_w};
+    t = V3{t.x * ratio, t.y * ratio, t.z * ratio};
+    o = V3{o.x + t.x, o.y + t.y, o.z + t.z};
+    t = V3{U.x * b, U.y * b, U.z * b};
+    t = V3{t.x * f.cam->ortho_h, t.y * f.cam->ortho_h, t.z * f.cam->ortho_h};
+    o = V3{o.x + t.x, o.y + t.y, o.z + t.z};
+    return o;
+}
+
 V3 shade(const Frame& f, V3 cam, V3 n, V3 pos, int& extra_steps, Tally* tl) {
     const V3 L{f.env->light_dir[0], f.env->light_dir[1], f.env->light_dir[2]};
     const V3 LC{f.env->light_color[0], f.env->light_color[1], f.env->light_color[2]};
@@ -115,8 +135,9 @@ void pixel(const Frame& f, int tx, int ty, Tally* tl = nullptr) {
     }
     if ((uint32_t)x >= f.W || (uint32_t)y >= f.H) return;
     const int W = (int)f.W, H = (int)f.H;
-    const V3 origin{f.cam->origin[0], f.cam->origin[1], f.cam->origin[2]};
-    const V3 rd = primary_dir(f, x, y);
+    const bool orth = ortho(f);
+    const V3 origin = orth ? ortho_origin(f, x, y) : V3{f.cam->origin[0], f.cam->origin[1], f.cam->origin[2]};
+    const V3 rd = orth ? V3{f.cam->fwd[0], f.cam->fwd[1], f.cam->fwd[2]} : primary_dir(f, x, y);
     MarchOut m;
     const bool hit = march(*f.w, origin, rd, f.o->norm_mode, kMaxSteps, m);
     int steps = m.steps;

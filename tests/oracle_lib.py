@@ -25,7 +25,8 @@ class Hits(C.Structure):
 
 class Camera(C.Structure):
     _fields_ = [("origin", C.c_float * 3), ("fwd", C.c_float * 3), ("up", C.c_float * 3),
-                ("right", C.c_float * 3), ("fov_deg", C.c_float), ("tan_half", C.c_float)]
+                ("right", C.c_float * 3), ("fov_deg", C.c_float), ("tan_half", C.c_float),
+                ("ortho_w", C.c_float), ("ortho_h", C.c_float)]
 
 
 class Env(C.Structure):
@@ -198,7 +199,7 @@ def get_directions(euler):
     return f, u, r
 
 
-def make_camera(origin, euler, fov_deg=90.0, tan_half=0.0):
+def make_camera(origin, euler, fov_deg=90.0, tan_half=0.0, ortho=None):
     f, u, r = get_directions(euler)
     cam = Camera()
     cam.origin[:] = [float(v) for v in origin]
@@ -207,6 +208,7 @@ def make_camera(origin, euler, fov_deg=90.0, tan_half=0.0):
     cam.right[:] = r.tolist()
     cam.fov_deg = fov_deg
     cam.tan_half = tan_half
+    cam.ortho_w, cam.ortho_h = (float(ortho[0]), float(ortho[1])) if ortho else (0.0, 0.0)  # SetOrthoWindowSize, ORTHO build
     return cam
 
 

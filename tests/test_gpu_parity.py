@@ -177,6 +177,35 @@ def test_render_matches_oracle(vx, gpu_worlds, mode):
     rt.close()
 
 
+@pytest.mark.parametrize("mode", [dict(checkerboard=0, debug_view=0, shadows=1), dict(checkerboard=1, debug_view=1, shadows=0),
+                                  dict(checkerboard=0, debug_view=0, shadows=0)])
+def test_ortho_render_matches_oracle(vx, gpu_worlds, mode):
+    """Orthographic camera (getRayDirectionOrtho, Renderer.cu:61-70): per-pixel origins, rays along fwd; shading and the
+    debug distance use the pixel's own origin.  Same criteria as the perspective test; dense and fused shading agree."""
+    dims, org = (128, 64, 128), (512, 0, 256)
+    w = gpu_worlds(dims, org, 8)
+    ow = worlds.oracle_world(dims, org, 8)
+    W, H = 256, 144
+    euler, cam_pos, size = (-0.7, 0.3, 0.0), (64, 110, 120), (40.0, 30.0)
+    cam = vx.make_camera(cam_pos, euler, 90.0, ortho=size)
+    ocam = ol.make_camera(cam_pos, euler, 90.0, tan_half=1.0, ortho=size)
+    opts = vx.RenderOpts(mode["checkerboard"], 2, mode["debug_view"], mode["shadows"], 1, vx.NORM_HOST, 0, 0, 0, 0, None)
+    oopts = ol.RenderOpts(mode["checkerboard"], 2, mode["debug_view"], mode["shadows"], 1, ol.NORM_HOST)
+    rt = vx.VoxelRaytracer3D(w, 1)
+    seed = np.full((H, W, 4), 7, np.uint8)
+    ref, rsteps = ow.render(ocam, ol.default_env(), oopts, W, H, bgra=seed.copy())
+    for fused in (0, 1):
+        rt.set_fused_shade(fused)
+        got = rt.render_host(cam, vx.default_env(), opts, W, H, bgra=seed.copy())
+        assert np.array_equal((got != 7).any(2) | (got[..., 3] == 255), (ref != 7).any(2) | (ref[..., 3] == 255))
+        diff = np.abs(got.astype(np.int16) - ref.astype(np.int16))
+        assert diff.max() <= 1, "max channel difference %d" % diff.max()
+        assert (diff > 0).mean() < 0.01
+    hit_share = ((ref[..., :3] != 7).any(2)).mean()
+    assert hit_share > 0.3
+    rt.close()
+
+
 def test_full_scale_frame_matches_oracle(vx):
     """BASELINE config 2 scale: 1024x256x1024 world built on the device, handed to the oracle in the
     reference's form; whole shaded + shadowed frame: identical written pixels, RGB within 1/255, and the

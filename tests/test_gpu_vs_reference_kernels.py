@@ -89,3 +89,29 @@ def test_frame_equals_reference_screen_dispatch(vx, my_world, tmp_path, view):
     assert (ref != 255).any(), "reference frame is empty"
     assert np.array_equal(got, ref), "differing pixels: %d" % int((got != ref).any(2).sum())
     rt.close()
+
+
+REF_ORTHO = os.path.join(ol.ORACLE_DIR, "_ref", "ref_gpu_nofma_ortho")
+
+
+@pytest.mark.skipif(not os.path.exists(REF_ORTHO), reason="oracle/_ref/ref_gpu_nofma_ortho not built")
+@pytest.mark.parametrize("view", [((128, 150, 300), (-0.6, 0.0, 0.0), (100.0, 60.0)), ((40, 100, 40), (-0.9, 2.2, 0.0), (10.0, 10.0))])
+def test_ortho_frame_equals_reference_ortho_build(vx, my_world, tmp_path, view):
+    """The reference built with -DORTHO (getRayDirectionOrtho, Renderer.cu:61-70,202-204): as shipped otherwise
+    (checkerboard, DEBUG_VIEW quadrants, crosshair); vx_camera.ortho_w / ortho_h select the same camera here."""
+    pos, eul, size = view
+    W, H = 320, 180
+    out = tmp_path / "frame.bgra"
+    res = subprocess.run([REF_ORTHO] + [str(a) for a in ["render", *DIMS, FACTOR, W, H, *pos, *eul, 1, out, *size]],
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    ref = np.fromfile(out, np.uint8).reshape(H, W, 4)
+    rt = vx.VoxelRaytracer3D(my_world, 1)
+    cam = vx.make_camera(pos, eul, 90.0, ortho=size)
+    opts = vx.RenderOpts(1, 0, 1, 0, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None)
+    got = rt.render_host(cam, vx.default_env(), opts, W, H, bgra=np.full((H, W, 4), 255, np.uint8))
+    assert (ref != 255).any(), "reference frame is empty"
+    assert np.array_equal(got, ref), "differing pixels: %d" % int((got != ref).any(2).sum())
+    persp = rt.render_host(vx.make_camera(pos, eul, 90.0), vx.default_env(), opts, W, H, bgra=np.full((H, W, 4), 255, np.uint8))
+    assert not np.array_equal(persp, ref)
+    rt.close()

@@ -132,3 +132,33 @@ def test_step_cap_against_reference():
     st = np.zeros(n, np.int32)
     ref.vxref_trace(rw, o, d, n, 8, hit.ctypes.data, pos, nrm, st.ctypes.data, 0)
     assert np.array_equal(hit, r["hit"]) and np.array_equal(st, r["steps"])
+
+
+def test_ortho_camera_is_the_batch_trace_of_its_rays():
+    """getRayDirectionOrtho (Renderer.cu:61-70): the oracle's orthographic frame has, pixel for pixel, the step counts of
+    its own batch march over rays built here independently: origin + right*(u*2-1)*size.x*ratio + up*(v*2-1)*size.y in
+    float32, left to right, direction = fwd.  (The GPU test against the reference's -DORTHO build pins the camera.)"""
+    dims, org = (128, 64, 128), (512, 0, 256)
+    w = worlds.oracle_world(dims, org, 8)
+    W, H, size = 96, 54, (40.0, 30.0)
+    pos, eul = (64, 110, 120), (-0.7, 0.3, 0.0)
+    cam = ol.make_camera(pos, eul, 90.0, tan_half=1.0, ortho=size)
+    opts = ol.RenderOpts(0, 0, 1, 0, 0, ol.NORM_HOST)
+    _, steps = w.render(cam, ol.default_env(), opts, W, H)
+    f, u, r = ol.get_directions(eul)
+    f32 = np.float32
+    ys, xs = np.mgrid[0:H, 0:W]
+    a = (xs.astype(f32) / f32(W) * f32(2) - f32(1)).astype(f32)
+    b = (ys.astype(f32) / f32(H) * f32(2) - f32(1)).astype(f32)
+    ratio = f32(W) / f32(H)
+    o = np.empty((H, W, 3), f32)
+    for k in range(3):
+        t = ((r[k] * a).astype(f32) * f32(size[0])).astype(f32) * ratio
+        t2 = (u[k] * b).astype(f32) * f32(size[1])
+        o[..., k] = (f32(pos[k]) + t.astype(f32)).astype(f32) + t2.astype(f32)
+    d = np.broadcast_to(f, (H * W, 3)).copy()
+    res = w.trace(o.reshape(-1, 3), d, norm_mode=ol.NORM_HOST)
+    assert np.array_equal(res["steps"].reshape(H, W), steps)
+    assert 0.2 < res["hit"].mean() < 1.0
+    persp = w.render(ol.make_camera(pos, eul, 90.0, tan_half=1.0), ol.default_env(), opts, W, H)[1]
+    assert not np.array_equal(persp, steps)

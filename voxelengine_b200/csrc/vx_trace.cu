@@ -86,6 +86,8 @@ __global__ void __launch_bounds__(128, VX_TRACE_MIN_BLOCKS) trace_rays(WorldView
 struct FrameParams {
     V3 origin, fwd, up, right;
     V3 start0;                 // origin / factor (IEEE division, done once on the host)
+    float ortho_w, ortho_h;    // > 0: orthographic window (getRayDirectionOrtho, Renderer.cu:61-70), else perspective
+    float factor_f;
     V3 light, light_color, ambient;
     float tan_half;
     uint32_t W, H;
@@ -105,9 +107,22 @@ __device__ __forceinline__ void put_pixel(uint8_t* __restrict__ bgra, uint32_t W
     reinterpret_cast<uint32_t*>(bgra)[(size_t)y * W + x] = b | (g << 8) | (r << 16) | 0xFF000000u;
 }
 
+// The origin screenDispatch traces pixel (x, y) from, and shades with: the camera, or in the ORTHO build (Renderer.cu:202-204)
+// getRayDirectionOrtho's origin += right * (u*2-1) * size.x * ratio; origin += up * (v*2-1) * size.y (:61-70; float3 * float
+// products left to right)
+__device__ __forceinline__ V3 pixel_origin(const FrameParams& f, bool ortho, int x, int y) {
+    if (!ortho) return f.origin;
+    const float a = fsub(fmul(fdiv((float)x, (float)(int)f.W), 2.0f), 1.0f), b = fsub(fmul(fdiv((float)y, (float)(int)f.H), 2.0f), 1.0f);
+    const float ratio = fdiv((float)f.W, (float)f.H);
+    V3 t = mk(fmul(fmul(fmul(f.right.x, a), f.ortho_w), ratio), fmul(fmul(fmul(f.right.y, a), f.ortho_w), ratio), fmul(fmul(fmul(f.right.z, a), f.ortho_w), ratio));
+    V3 o = mk(fadd(f.origin.x, t.x), fadd(f.origin.y, t.y), fadd(f.origin.z, t.z));
+    t = mk(fmul(fmul(f.up.x, b), f.ortho_h), fmul(fmul(f.up.y, b), f.ortho_h), fmul(fmul(f.up.z, b), f.ortho_h));
+    return mk(fadd(o.x, t.x), fadd(o.y, t.y), fadd(o.z, t.z));
+}
+
 // calculateColor, Renderer.cu:90-168 (AO block: samples = 0, no-op) with the shadow result supplied, then Tonemap (:170-177)
 template <int NORM>
-__device__ __forceinline__ V3 shade(const FrameParams& f, V3 n, V3 pos, bool shadowed) {
+__device__ __forceinline__ V3 shade(const FrameParams& f, V3 cam, V3 n, V3 pos, bool shadowed) {
     const float nl = dot3(n, f.light);
     const float ldot = fmul(fmaxf(nl, 0.0f), shadowed ? 0.0f : 1.0f);
     const float up_dot = dot3(n, mk(0.0f, 1.0f, 0.0f));
@@ -116,7 +131,7 @@ __device__ __forceinline__ V3 shade(const FrameParams& f, V3 n, V3 pos, bool sha
     V3 c = mk(fadd(fmul(ldot, f.light_color.x), fmul(f.ambient.x, amb)), fadd(fmul(ldot, f.light_color.y), fmul(f.ambient.y, amb)),
               fadd(fmul(ldot, f.light_color.z), fmul(f.ambient.z, amb)));
     if (!shadowed) {
-        const V3 view = normalize3<NORM>(mk(fsub(pos.x, f.origin.x), fsub(pos.y, f.origin.y), fsub(pos.z, f.origin.z)));
+        const V3 view = normalize3<NORM>(mk(fsub(pos.x, cam.x), fsub(pos.y, cam.y), fsub(pos.z, cam.z)));
         const V3 refl = mk(fsub(f.light.x, fmul(fmul(2.0f, n.x), nl)), fsub(f.light.y, fmul(fmul(2.0f, n.y), nl)),
                            fsub(f.light.z, fmul(fmul(2.0f, n.z), nl)));
         const float spec = powf(fmaxf(dot3(view, refl), 0.0f), 32.0f);
@@ -160,15 +175,16 @@ __device__ __forceinline__ void add_stats(unsigned long long* __restrict__ stats
 
 // Everything screenDispatch does once the rays of a pixel are known (Renderer.cu:203-275).
 template <int NORM>
-__device__ __forceinline__ void emit_pixel(const FrameParams& f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane, uint32_t pix,
+__device__ __forceinline__ void emit_pixel(const FrameParams& f, bool ortho, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane, uint32_t pix,
                                            bool hit, V3 pos, uint32_t ncode, bool shadowed, int steps, V3 miss_dir) {
     const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
     const int W = (int)f.W, H = (int)f.H;
     if (hit) {
         const V3 nn = normal_from_code(ncode);
         const V3 n = mk(-nn.x, -nn.y, -nn.z);
+        const V3 cam = pixel_origin(f, ortho, x, y);
         if (f.debug_view) { // Renderer.cu:215-243
-            const V3 dl = mk(fsub(pos.x, f.origin.x), fsub(pos.y, f.origin.y), fsub(pos.z, f.origin.z));
+            const V3 dl = mk(fsub(pos.x, cam.x), fsub(pos.y, cam.y), fsub(pos.z, cam.z));
             const float dist = __fsqrt_rn(dot3(dl, dl));
             const float md = (float)(1.0 + kEpsDDA);
             const V3 hp = mk(fmodf(fdiv(pos.x, 128.0f), md), fmodf(fdiv(pos.y, 128.0f), md), fmodf(fdiv(pos.z, 128.0f), md));
@@ -177,7 +193,7 @@ __device__ __forceinline__ void emit_pixel(const FrameParams& f, uint8_t* __rest
             else if (x < (W >> 1)) {}
             else put_pixel(bgra, f.W, f.H, x, y, mk(fmul(dist, 0.01f), 0.0f, 0.0f));
         } else {
-            put_pixel(bgra, f.W, f.H, x, y, shade<NORM>(f, n, pos, shadowed));
+            put_pixel(bgra, f.W, f.H, x, y, shade<NORM>(f, cam, n, pos, shadowed));
         }
     } else {
         put_pixel(bgra, f.W, f.H, x, y, miss_dir); // miss: colour = ray direction, Renderer.cu:254-258
@@ -187,7 +203,7 @@ __device__ __forceinline__ void emit_pixel(const FrameParams& f, uint8_t* __rest
     if (steps_plane) steps_plane[(size_t)y * f.W + x] = steps;
 }
 
-template <int NORM, bool STATS>
+template <int NORM, bool STATS, bool ORTHO>
 struct PrimaryPolicy {
     static constexpr bool kDrain = false;
     static constexpr int kRefill = 32; // a warp takes a whole tile at a time: neighbouring rays stay in step (2.2 ms instead of
@@ -255,6 +271,11 @@ struct PrimaryPolicy {
         }
         if ((uint32_t)x >= f.W || (uint32_t)y >= f.H) return;
         pix = (uint32_t)x | ((uint32_t)y << 15) | ((f.crosshair && tx == (f.W >> 1) && ty == (f.H >> 1)) ? (1u << 30) : 0u);
+        if (ORTHO) { // every ray runs along fwd (normalised by Raytrace only), from its own origin
+            const V3 o = pixel_origin(f, true, x, y);
+            lane_setup(w, L, mk(fdiv(o.x, f.factor_f), fdiv(o.y, f.factor_f), fdiv(o.z, f.factor_f)), normalize3<NORM>(f.fwd), 0u);
+            return;
+        }
         // Raytrace normalises the (already normalised) direction it is given once more (VolumeRaytracer.cu:363)
         lane_setup(w, L, f.start0, normalize3<NORM>(primary_dir(x, y)), 0u);
     }
@@ -271,7 +292,7 @@ struct PrimaryPolicy {
             pix |= 0x80000000u;
         } else {
             const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
-            emit_pixel<NORM>(f, bgra, steps_plane, pix, hit, pos, ncode, false, L.total, hit ? pos : primary_dir(x, y));
+            emit_pixel<NORM>(f, ORTHO, bgra, steps_plane, pix, hit, pos, ncode, false, L.total, hit ? pos : (ORTHO ? f.fwd : primary_dir(x, y)));
         }
         L.flags = ST_IDLE;
     }
@@ -368,7 +389,7 @@ struct ShadowPolicy {
             const uint2 e = list[(head + (threadIdx.x & 31u)) & (kShadeList - 1u)];
             const float4 r = q.rec[e.x];
             const uint32_t a = q.aux[e.x];
-            emit_pixel<NORM>(f, bgra, steps_plane, __float_as_uint(r.w), true, mk(r.x, r.y, r.z), a >> 16, (e.y >> 31) != 0u,
+            emit_pixel<NORM>(f, f.ortho_w > 0.0f, bgra, steps_plane, __float_as_uint(r.w), true, mk(r.x, r.y, r.z), a >> 16, (e.y >> 31) != 0u,
                              (int)(a & 0xFFFFu) + (int)(e.y & 0x7FFFFFFFu), mk(0.0f, 0.0f, 0.0f));
         }
         __syncwarp();
@@ -399,7 +420,7 @@ __global__ void __launch_bounds__(256) shade_pixels(FrameParams f, uint8_t* __re
             wk.E = q.aux[i + 4 * f.ids] + q.aux[i + 7 * f.ids];
             add_stats(stats, 0u, 0u, 1u, shadowed, (uint32_t)steps, wk);
         }
-        emit_pixel<NORM>(f, bgra, steps_plane, __float_as_uint(r.w), true, mk(r.x, r.y, r.z), a >> 16, shadowed, steps, mk(0.0f, 0.0f, 0.0f));
+        emit_pixel<NORM>(f, f.ortho_w > 0.0f, bgra, steps_plane, __float_as_uint(r.w), true, mk(r.x, r.y, r.z), a >> 16, shadowed, steps, mk(0.0f, 0.0f, 0.0f));
     }
 }
 
@@ -443,12 +464,12 @@ __global__ void __launch_bounds__(256) bounce_setup(FrameParams f, ShadowQueue q
     }
 }
 
-template <int NORM, bool STATS>
+template <int NORM, bool STATS, bool ORTHO>
 __global__ void __launch_bounds__(128, VX_MIN_BLOCKS) primary_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
                                                                    unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
     __shared__ float4 stage_rec[128];
     __shared__ uint32_t stage_aux[STATS ? 512 : 128];
-    PrimaryPolicy<NORM, STATS> pol(f, bgra, steps_plane, stats, q);
+    PrimaryPolicy<NORM, STATS, ORTHO> pol(f, bgra, steps_plane, stats, q);
     pol.stage_rec = stage_rec; pol.stage_aux = stage_aux;
     run_lanes<false, STATS>(w, pol, next);
 }
@@ -641,6 +662,8 @@ static int fill_frame(vx_tracer* t, const vx_camera* cam, const vx_env* env, con
     f.origin = V3{cam->origin[0], cam->origin[1], cam->origin[2]};
     const float ff = (float)t->world->factor;
     f.start0 = V3{cam->origin[0] / ff, cam->origin[1] / ff, cam->origin[2] / ff}; // start = origin / factor, VolumeRaytracer.cu:361
+    const bool ortho = cam->ortho_w > 0.0f && cam->ortho_h > 0.0f;
+    f.ortho_w = ortho ? cam->ortho_w : 0.0f; f.ortho_h = ortho ? cam->ortho_h : 0.0f; f.factor_f = ff;
     f.fwd = V3{cam->fwd[0], cam->fwd[1], cam->fwd[2]};
     f.up = V3{cam->up[0], cam->up[1], cam->up[2]};
     f.right = V3{cam->right[0], cam->right[1], cam->right[2]};
@@ -723,9 +746,16 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     // optional per-kernel timing (vx_tracer_set_timing): events between the launches, on the launching stream
 #define VX_MARK(i) do { if (t->timing) VX_CUDA(cudaEventRecord(t->ev[i], cs)); } while (0)
     t->timed_kernels = 0;
-#define VX_LAUNCH(N, S) do { rc = persistent_blocks(t, primary_rays<N, S>, f.ids, blocks); if (rc) return rc; \
-        VX_MARK(0); \
-        primary_rays<N, S><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); \
+#define VX_LAUNCH(N, S) do { \
+        if (f.ortho_w > 0.0f) { \
+            rc = persistent_blocks(t, primary_rays<N, S, true>, f.ids, blocks); if (rc) return rc; \
+            VX_MARK(0); \
+            primary_rays<N, S, true><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); \
+        } else { \
+            rc = persistent_blocks(t, primary_rays<N, S, false>, f.ids, blocks); if (rc) return rc; \
+            VX_MARK(0); \
+            primary_rays<N, S, false><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); \
+        } \
         VX_MARK(1); t->timed_kernels = 1; \
         if (shadow_pass && !t->primary_only) { \
             shadow_setup<N><<<dense_blocks, 256, 0, cs>>>(w, f, q); \
