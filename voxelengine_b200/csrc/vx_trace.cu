@@ -856,9 +856,10 @@ extern "C" int vx_render_host(vx_tracer* t, const vx_camera* cam, const vx_env* 
         VX_CUDA(cudaMemcpyAsync(t->d_frame, h_bgra, bytes, cudaMemcpyHostToDevice, t->stream));
     }
     // Large plain frames are rendered in horizontal slices so that the copy of one slice to the host overlaps the render of
-    // the next (second stream, one event per slice).  Two slices measured best at 4K (e2e 3975 -> 4060 Mrays/s; three and
-    // four lose more to launch tails than they hide, and letting the kernels store pixels straight into pinned host
-    // memory over PCIe is far slower: 2480 Mrays/s).  VX_HOST_SLICES=1..4 overrides.  Checkerboard frames (rows of neighbouring threads interleave) and
+    // the next (second stream, one event per slice).  Two uneven slices measured best at 4K: the first 80 % of the rows, then
+    // the rest, so that only a fifth of the frame is still to be copied when the last kernel ends (ms per frame: one pass
+    // 3.44, 50/50 3.33, 70/30 3.18, 80/20 3.10, 90/10 3.12; three even slices 3.47 — more slices lose more to launch tails
+    // than they hide; letting the kernels store pixels straight into pinned host memory over PCIe is far slower).  VX_HOST_SLICES=1..4 overrides.  Checkerboard frames (rows of neighbouring threads interleave) and
     // callers that already partition the frame take the single-pass path.
     static const uint32_t kSlices = [] { const char* e = getenv("VX_HOST_SLICES"); int v = e ? atoi(e) : 2; return (uint32_t)(v < 1 ? 1 : (v > 4 ? 4 : v)); }();
     const bool sliced = opts && !opts->checkerboard && opts->tile_w == 0 && opts->tile_h == 0 && opts->band_count == 0 && kSlices > 1 && H >= 64u * kSlices;
@@ -873,8 +874,11 @@ extern "C" int vx_render_host(vx_tracer* t, const vx_camera* cam, const vx_env* 
         VX_CUDA(cudaStreamCreateWithFlags(&t->copy_stream, cudaStreamNonBlocking));
         for (uint32_t k = 0; k < kSlices; ++k) VX_CUDA(cudaEventCreateWithFlags(&t->slice_ev[k], cudaEventDisableTiming));
     }
-    const uint32_t rows = ((H + kSlices - 1) / kSlices + 7u) / 8u * 8u;
-    for (uint32_t k = 0, y0 = 0; y0 < H; ++k, y0 += rows) {
+    static const float kSplit = [] { const char* e = getenv("VX_HOST_SPLIT"); float v = e ? (float)atof(e) : 0.8f; return v < 0.1f ? 0.1f : (v > 0.97f ? 0.97f : v); }();
+    const uint32_t even_rows = ((H + kSlices - 1) / kSlices + 7u) / 8u * 8u;
+    for (uint32_t k = 0, y0 = 0, rows = 0; y0 < H; ++k, y0 += rows) {
+        // two slices: the first takes kSplit of the rows, so that less of the frame is left to copy after the last kernel
+        rows = kSlices == 2 ? (k == 0 ? ((uint32_t)((float)H * kSplit) + 7u) / 8u * 8u : H - y0) : even_rows;
         vx_render_opts o = *opts;
         o.tile_x0 = 0; o.tile_y0 = y0; o.tile_w = (W + 31u) / 32u * 32u; o.tile_h = rows;
         int rc = vx_render(t, cam, env, &o, t->d_frame, nullptr, W, H, t->stream);
