@@ -4,7 +4,7 @@ ARCH   := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS := -std=c++17 -O3 $(ARCH) -lineinfo -fmad=false -Xcompiler -fPIC -Xptxas -v
 CSRC   := voxelengine_b200/csrc
 LIB    := voxelengine_b200/lib/libvxrt.so
-SRCS   := $(CSRC)/vx_world.cu $(CSRC)/vx_trace.cu $(CSRC)/vx_shared.cu
+SRCS   := $(CSRC)/vx_world.cu $(CSRC)/vx_trace.cu $(CSRC)/vx_shared.cu $(CSRC)/vx_edit.cu
 HDRS   := $(CSRC)/vx_device.cuh $(CSRC)/vx_march.cuh $(CSRC)/vx_noise.cuh $(CSRC)/vx_host.h include/vxrt.h
 
 all: $(LIB)

@@ -85,6 +85,17 @@ int vx_world_get_info(const vx_world* w, vx_world_info* info);
  * words), per-brick masks indexed by coarse tiled index (bricks * factor^3/32 words, zeros for
  * empty bricks) and per-brick bounds (bricks * 6 floats: min xyz, max xyz; 0,0,0,-1,-1,-1 when
  * empty) — exactly what GenerateLowresVoxelBuffer returns.  Any pointer may be NULL. */
+/* Editing and storing a built world (the reference README's "modifiable terrain" / streaming items; the
+ * reference can only flip bits of the dense grid through BitRef::operator=, VolumeRaytracer.cu:19-36, and rebuild).
+ * vx_world_edit sets (solid != 0) or clears the n voxels voxels_xyz[3*i..] (host array; coordinates outside the world
+ * are ignored, duplicates are fine) and refreshes the touched bricks' masks, bounds and top-level bits on the device:
+ * afterwards the world is bit for bit what vx_world_from_dense_bits would build from the edited dense grid.
+ * Synchronous; waits for work in flight on the device first (the brick pool may move).
+ * vx_world_save / vx_world_load: the built brickmap as one file ("VXBRICK1": header, top-level bits, padded traversal
+ * grid, brick records, mask pool, FNV-1a checksum); a loaded world traces and edits like the one that was saved. */
+int vx_world_edit(vx_world* w, const uint32_t* voxels_xyz, size_t n, int solid);
+int vx_world_save(const vx_world* w, const char* path);
+int vx_world_load(vx_world** out, const char* path, int device);
 int vx_world_download(const vx_world* w, uint32_t* top_words, uint32_t* brick_words, float* bounds6);
 
 /* ------------------------------------------------------------------------------------------

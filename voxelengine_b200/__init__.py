@@ -69,6 +69,7 @@ ABI_SYMBOLS = [
     "vx_render_host", "vx_bounce_rays", "vx_tracer_set_timing", "vx_tracer_set_fused_shade", "vx_tracer_frame_times", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
     "vx_shared_alloc", "vx_shared_open", "vx_shared_close", "vx_shared_free", "vx_device_to_host",
     "vx_host_register", "vx_host_unregister", "vx_bands_to_host",
+    "vx_world_edit", "vx_world_save", "vx_world_load",
 ]
 
 _lib = None
@@ -113,6 +114,9 @@ def lib():
     L.vx_shared_close.argtypes = [vp, i32]
     L.vx_shared_free.argtypes = [vp, i32]
     L.vx_device_to_host.argtypes = [vp, vp, sz, i32, vp]
+    L.vx_world_edit.argtypes = [vp, vp, sz, i32]
+    L.vx_world_save.argtypes = [vp, C.c_char_p]
+    L.vx_world_load.argtypes = [C.POINTER(vp), C.c_char_p, i32]
     L.vx_host_register.argtypes = [vp, sz]
     L.vx_host_unregister.argtypes = [vp]
     L.vx_bands_to_host.argtypes = [vp, vp, u32, u32, u32, u32, i32, vp]
@@ -247,6 +251,22 @@ class World:
         h = C.c_void_p()
         _check(lib().vx_world_from_dense_bits(C.byref(h), b.ctypes.data, X, Y, Z, factor, device))
         return cls(h)
+
+    @classmethod
+    def load(cls, path, device=0):
+        """A world written by save()."""
+        h = C.c_void_p()
+        _check(lib().vx_world_load(C.byref(h), os.fsencode(path), device))
+        return cls(h)
+
+    def save(self, path):
+        _check(lib().vx_world_save(self.h, os.fsencode(path)))
+
+    def edit(self, voxels, solid=True):
+        """Set (or clear) the voxels (n x 3 integer coordinates) in place: masks, bounds and top-level bits of the touched
+        bricks are refreshed on the device; the result equals a rebuild from the edited dense grid."""
+        v = np.ascontiguousarray(voxels, np.uint32).reshape(-1, 3)
+        _check(lib().vx_world_edit(self.h, v.ctypes.data, v.shape[0], 1 if solid else 0))
 
     def close(self):
         if self.h:

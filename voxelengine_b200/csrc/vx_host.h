@@ -59,7 +59,8 @@ struct vx_world {
     uint2* d_records = nullptr;  // nbricks, tiled order (build-time only; freed once the padded copy exists)
     uint32_t* d_ptop = nullptr;  // padded linear occupancy bits (traversal)
     uint2* d_precords = nullptr; // padded linear records (traversal)
-    uint32_t* d_pool = nullptr;  // occupied * words_per_brick
+    uint32_t* d_pool = nullptr;  // pool_capacity * words_per_brick; slots >= pool_used are zero
+    uint64_t pool_capacity = 0, pool_used = 0; // in bricks; vx_world_edit hands out slots pool_used.. and grows the pool
     float build_ms = 0.0f;
     vx::WorldView view() const {
         vx::WorldView v;

@@ -322,6 +322,8 @@ static int finish_build(vx_world* w, const uint32_t* d_tmp, const BuildGeom& g) 
     w->occupied = h[1];
     const size_t pool_words = (size_t)(w->occupied ? w->occupied : 1) * words;
     VX_CUDA(cudaMalloc(&w->d_pool, pool_words * 4));
+    w->pool_capacity = w->occupied ? w->occupied : 1; w->pool_used = w->occupied;
+    if (!w->occupied) VX_CUDA(cudaMemset(w->d_pool, 0, pool_words * 4));
     const uint64_t total_words = (uint64_t)nb * words;
     compact_bricks<<<(uint32_t)((total_words / 4 + 255) / 256), 256>>>(d_tmp, w->d_records, w->d_pool, words, total_words);
     VX_CUDA(cudaGetLastError());
