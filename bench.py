@@ -327,9 +327,20 @@ def run_ours(args, wl, wl_name):
         hostframe = HostFrame(part, dev)
         local = frame if frame is not None else part.alloc_frame("cuda")
 
+        e2e_opts = {}
+
+        def e2e_rows(y0, h):
+            o = e2e_opts.get((y0, h))
+            if o is None:
+                o = e2e_opts[(y0, h)] = vx.RenderOpts(0, 0, 0, 1, 1, vx.NORM_DEVICE, 0, y0, cols, h, None, band_count, band_index)
+            rt.render_device(cam, env, o, local.data_ptr(), W, H, stream=stream)
+
         def e2e_step():
-            rt.render_device(cam, env, o_timed, local.data_ptr(), W, H, stream=stream)
-            hostframe.store(local.data_ptr(), stream)
+            if args.host_split >= 1.0:
+                rt.render_device(cam, env, o_timed, local.data_ptr(), W, H, stream=stream)
+                hostframe.store(local.data_ptr(), stream)
+            else:
+                hostframe.render_and_store(e2e_rows, local.data_ptr(), args.host_split)
             hostframe.fence()
         e2e_step()
         dist.barrier()
@@ -388,6 +399,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--exchange", default=os.environ.get("VX_EXCHANGE", "shared"), choices=["shared", "gather"],
                     help="N > 1: how the bands reach rank 0 (shared: peer stores into rank 0's frame; gather: NCCL gather)")
+    ap.add_argument("--host-split", type=float, default=float(os.environ.get("VX_HOST_SPLIT_N", "0.8")),
+                    help="N > 1, e2e: share of the rows rendered before the first copy to the host starts (1 = no overlap)")
     ap.add_argument("--gather-chunks", type=int, default=int(os.environ.get("VX_GATHER_CHUNKS", "1")),
                     help="N > 1: row chunks of the frame whose gather overlaps the next chunk's render (1 = render, then gather)")
     args = ap.parse_args()

@@ -55,6 +55,18 @@ def _worker(rank, world_size, port, out_path):
     if rank == 0:
         np.save(out_path + ".host.npy", np.array(hf.array).reshape(-1))
     hf.fence()
+    # the overlapped variant: two row ranges, the first one's copy on a second stream
+    hf.array[:] = 3
+    hf.fence()
+    cols = (W + 31) // 32 * 32
+
+    def render_rows(y0, rows):
+        rt.render_device(cam, vx.default_env(), vx.RenderOpts(0, 1, 0, 1, 1, vx.NORM_DEVICE, 0, y0, cols, rows, None, bc, bi), mine.data_ptr(), W, H)
+    hf.render_and_store(render_rows, mine.data_ptr(), 0.6)
+    hf.fence()
+    if rank == 0:
+        np.save(out_path + ".host2.npy", np.array(hf.array).reshape(-1))
+    hf.fence()
     hf.close()
     rt.close()
     dist.destroy_process_group()
@@ -70,6 +82,7 @@ def test_ranks_render_into_rank0_frame(tmp_path, world_size):
     assert want.any()
     assert np.array_equal(got, want)
     assert np.array_equal(np.load(out + ".host.npy"), want)  # H = 203: the last band is ragged
+    assert np.array_equal(np.load(out + ".host2.npy"), want)
 
 
 def test_shared_handle_validation():

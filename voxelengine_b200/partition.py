@@ -214,15 +214,38 @@ class HostFrame:
         self.ptr = ctypes.addressof(self._view)
         vx.host_register(self.ptr, self.nbytes)
         self.array = np.frombuffer(self._map, np.uint8, part.H * part.W * 4).reshape(part.H, part.W, 4)
+        self._copy_stream = None
         if part.world_size > 1:
             dist.barrier(group=group)   # everyone has it mapped: the name can go
         if part.rank == 0:
             os.unlink(self.path)
 
-    def store(self, d_frame_ptr, stream=0):
-        """Enqueue the copy of this rank's bands from its device frame into the host frame (on `stream`)."""
+    def store(self, d_frame_ptr, stream=0, y0=0, rows=None):
+        """Enqueue the copy of this rank's bands from its device frame into the host frame (on `stream`); with y0 / rows
+        only the bands inside that row range (y0 a multiple of 8 * world_size, so the dealing of bands is unchanged)."""
         bc, bi = self.part.render_opts()
-        self._vx.bands_to_host(self.ptr, d_frame_ptr, self.part.W, self.part.H, bc, bi, self.device, stream)
+        rows = self.part.H - y0 if rows is None else rows
+        if y0 % (BAND_ROWS * max(bc, 1)):
+            raise ValueError("y0 must be a multiple of %d" % (BAND_ROWS * max(bc, 1)))
+        off = y0 * self.part.W * 4
+        self._vx.bands_to_host(self.ptr + off, d_frame_ptr + off, self.part.W, rows, bc, bi, self.device, stream)
+
+    def render_and_store(self, render_rows, d_frame_ptr, split=0.8):
+        """One frame to the host with the copy overlapped: render_rows(y0, rows) renders this rank's bands of the first
+        `split` of the rows (on the current stream), their copy runs on a second stream while the rest renders, and
+        only the last part's copy is left after the last kernel (same idea and measured split as vx_render_host)."""
+        n = max(self.part.world_size, 1) * BAND_ROWS
+        r0 = min(self.part.H, max(n, int(self.part.H * split) // n * n))
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(self.device)
+            self._events = [torch.cuda.Event(), torch.cuda.Event()]
+        for k, (y0, rows) in enumerate(((0, r0), (r0, self.part.H - r0))):
+            if rows <= 0:
+                continue
+            render_rows(y0, rows)
+            self._events[k].record()
+            self._copy_stream.wait_event(self._events[k])
+            self.store(d_frame_ptr, self._copy_stream.cuda_stream, y0, rows)
 
     def fence(self):
         """Every rank's copies enqueued so far have landed when this returns on every rank."""
