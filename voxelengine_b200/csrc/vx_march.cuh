@@ -289,6 +289,48 @@ done:
     o.ncode = axis == 3u ? 0u : (axis == 2u ? (oz ? 5u : 6u) : (axis == 1u ? (oy ? 3u : 4u) : (ox ? 1u : 2u)));
 }
 
+// What Raytrace does with the outcome of one brick march (VolumeRaytracer.cu:409-523): a hit ends the ray (ST_DONE + F_HIT,
+// result in pos/ncode); otherwise the start is re-seeded at the exit point with the reference's nudging rules (:438-489)
+// and the lane begins a new coarse traversal.  (qx,qy,qz) = the brick, (cx,cy,cz) = the traversal cell it was found in.
+template <bool BATCH>
+__device__ __forceinline__ void brick_done(const WorldView& w, Lane& L, const FineOut& q, int qx, int qy, int qz, int cx, int cy, int cz,
+                                           uint32_t next_axis, uint32_t hit_ncode, V3& pos, uint32_t& ncode) {
+    const float ff = (float)w.factor;
+    const float bx = fmul((float)qx, ff), by = fmul((float)qy, ff), bz = fmul((float)qz, ff);
+    L.total += q.steps; L.fsteps += q.steps;
+    const V3 hit_pos = mk(fadd(q.point.x, bx), fadd(q.point.y, by), fadd(q.point.z, bz));
+    if (q.hit) {
+        ncode = hit_ncode; // the slab test's normal if the brick march counted no step, else the last step's (:409-436)
+        pos = hit_pos;
+        if (L.total == 0) { // :515-523
+            pos = mk(fmul(L.s.x, ff), fmul(L.s.y, ff), fmul(L.s.z, ff));
+            ncode = (L.flags >> F_SN_SHIFT) & 7u;
+        }
+        if (BATCH) L.fcell = q.cell;
+        L.flags |= F_HIT;
+        lane_set_state(L, ST_DONE);
+        return;
+    }
+    V3 start = mk(fdiv(hit_pos.x, ff), fdiv(hit_pos.y, ff), fdiv(hit_pos.z, ff));
+    if (q.oob && qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) { // :438-489
+        start.x = nextafterf(start.x, L.d.x < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
+        start.y = nextafterf(start.y, L.d.y < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
+        start.z = nextafterf(start.z, L.d.z < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
+        if (qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) {
+            // NextCell of the COARSE traversal = the cell after its final advance (:347, :473)
+            const int sx = L.d.x > 0.0f ? 1 : -1, sy = L.d.y > 0.0f ? 1 : -1, sz = L.d.z > 0.0f ? 1 : -1;
+            const int nx = cx + (next_axis == 0u ? sx : 0), ny = cy + (next_axis == 1u ? sy : 0), nz = cz + (next_axis == 2u ? sz : 0);
+            const float gx = fsub((float)nx, start.x), gy = fsub((float)ny, start.y), gz = fsub((float)nz, start.z);
+            const float ax = fabsf(gx), ay = fabsf(gy), az = fabsf(gz);
+            if (ax < ay && ax < az) start.x = fadd(start.x, gx);
+            else if (ay < ax && ay < az) start.y = fadd(start.y, gy);
+            else start.z = fadd(start.z, gz);
+        }
+    }
+    L.s = start;
+    lane_set_state(L, ST_BEGIN);
+}
+
 // ST_CAND: the occupied cell L.bidx.  Tight-AABB slab test (VolumeRaytracer.cu:248-273); on a hit the brick is
 // marched (:409-436) and the lane either finishes (ST_DONE + F_HIT, result in pos/ncode) or re-seeds its start
 // (:438-489) and goes back to ST_BEGIN; on a slab miss it takes the step the reference takes and keeps going.
@@ -351,37 +393,7 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
         if (L.flags & F_CAPOK) fine_march8(mask, local, r, q);
         else fine_march<true>(mask, 8, local, r, q);
     } else fine_march<false>(mask, w.factor, local, r, q);
-    L.total += q.steps; L.fsteps += q.steps;
-    const V3 hit_pos = mk(fadd(q.point.x, bx), fadd(q.point.y, by), fadd(q.point.z, bz));
-    if (q.hit) {
-        ncode = q.steps == 0 ? sl.ncode : q.ncode;
-        pos = hit_pos;
-        if (L.total == 0) { // :515-523
-            pos = mk(fmul(L.s.x, ff), fmul(L.s.y, ff), fmul(L.s.z, ff));
-            ncode = (L.flags >> F_SN_SHIFT) & 7u;
-        }
-        if (BATCH) L.fcell = q.cell;
-        L.flags |= F_HIT;
-        lane_set_state(L, ST_DONE);
-        return;
-    }
-    V3 start = mk(fdiv(hit_pos.x, ff), fdiv(hit_pos.y, ff), fdiv(hit_pos.z, ff));
-    if (q.oob && qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) { // :438-489
-        start.x = nextafterf(start.x, L.d.x < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
-        start.y = nextafterf(start.y, L.d.y < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
-        start.z = nextafterf(start.z, L.d.z < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
-        if (qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) {
-            // NextCell of the COARSE traversal = the cell after its final advance (:347, :473)
-            const int nx = cx + (next_axis == 0u ? r.sx : 0), ny = cy + (next_axis == 1u ? r.sy : 0), nz = cz + (next_axis == 2u ? r.sz : 0);
-            const float gx = fsub((float)nx, start.x), gy = fsub((float)ny, start.y), gz = fsub((float)nz, start.z);
-            const float ax = fabsf(gx), ay = fabsf(gy), az = fabsf(gz);
-            if (ax < ay && ax < az) start.x = fadd(start.x, gx);
-            else if (ay < ax && ay < az) start.y = fadd(start.y, gy);
-            else start.z = fadd(start.z, gz);
-        }
-    }
-    L.s = start;
-    lane_set_state(L, ST_BEGIN);
+    brick_done<BATCH>(w, L, q, qx, qy, qz, cx, cy, cz, next_axis, q.steps == 0 ? sl.ncode : q.ncode, pos, ncode);
 }
 
 // One fast-loop step.  With no NaN among the tMax values (F_CAPOK) the reference's comparison chain (:293-322) picks the
