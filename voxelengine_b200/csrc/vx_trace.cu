@@ -11,8 +11,12 @@
 #ifndef VX_TRACE_MIN_BLOCKS
 #define VX_TRACE_MIN_BLOCKS 8 // same for the batch kernel (it carries the parity planes' counters too)
 #endif
+#ifndef VX_SHADOW_MIN_BLOCKS
+#define VX_SHADOW_MIN_BLOCKS VX_MIN_BLOCKS
+#endif
 #ifndef VX_MIN_BLOCKS
-#define VX_MIN_BLOCKS 8 // resident 128-thread blocks per SM the render kernels are compiled for (register budget)
+#define VX_MIN_BLOCKS 9 // resident 128-thread blocks per SM the render kernels are compiled for (56-register budget; measured
+                        // per 4K frame: 6 -> 2.96 ms, 7 -> 2.88, 8 -> 2.85, 9 -> 2.83, 10 (shadow_rays) -> 2.89)
 #endif
 
 namespace vx {
@@ -474,7 +478,7 @@ __global__ void __launch_bounds__(128, VX_MIN_BLOCKS) primary_rays(WorldView w, 
     run_lanes<false, STATS>(w, pol, next);
 }
 template <int NORM, bool STATS, bool FUSE>
-__global__ void __launch_bounds__(128, VX_MIN_BLOCKS) shadow_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
+__global__ void __launch_bounds__(128, VX_SHADOW_MIN_BLOCKS) shadow_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
                                                                   ShadowQueue q, unsigned long long* next) {
     __shared__ uint2 shade_list[FUSE ? 4 * kShadeList : 1];
     ShadowPolicy<NORM, STATS, FUSE> pol(f, q, bgra, steps_plane, shade_list + (FUSE ? (threadIdx.x >> 5) * kShadeList : 0u));
