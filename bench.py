@@ -193,7 +193,13 @@ def run_ours(args, wl, wl_name):
     stream = torch.cuda.current_stream().cuda_stream
     from voxelengine_b200.partition import FramePartition, SharedFrame
     part = FramePartition(W, H, world_size, rank)   # 8-row bands dealt round-robin over the ranks
-    shared = SharedFrame(part, dev) if world_size > 1 and args.exchange == "shared" else None
+    shared = None
+    if world_size > 1 and args.exchange == "shared":
+        try:
+            shared = SharedFrame(part, dev)
+        except RuntimeError as e:  # raised on every rank together: fall back to the NCCL gather
+            if rank == 0:
+                print("bench: shared frame unavailable (%s); using the NCCL gather" % e, file=sys.stderr)
     frame = part.alloc_frame("cuda") if shared is None else None
     if shared is not None and "VX_FUSED_SHADE" not in os.environ:
         shared.attach(rt)
@@ -324,8 +330,14 @@ def run_ours(args, wl, wl_name):
             shared.close()
             shared = None
         rt.set_fused_shade(0)
-        hostframe = HostFrame(part, dev)
         local = frame if frame is not None else part.alloc_frame("cuda")
+        try:
+            hostframe = HostFrame(part, dev)
+        except RuntimeError as e:  # every rank together: gather to rank 0, which copies the whole frame down
+            if rank == 0:
+                print("bench: shared host frame unavailable (%s); rank 0 copies the gathered frame" % e, file=sys.stderr)
+            frame = local
+            host = torch.empty(H * W * 4, dtype=torch.uint8).pin_memory() if rank == 0 else None
 
         e2e_opts = {}
 
@@ -336,6 +348,13 @@ def run_ours(args, wl, wl_name):
             rt.render_device(cam, env, o, local.data_ptr(), W, H, stream=stream)
 
         def e2e_step():
+            if hostframe is None:
+                rt.render_device(cam, env, o_timed, local.data_ptr(), W, H, stream=stream)
+                part.gather(local)
+                if rank == 0:
+                    host.copy_(local[: H * W * 4], non_blocking=True)
+                torch.cuda.synchronize()
+                return
             if args.host_split >= 1.0:
                 rt.render_device(cam, env, o_timed, local.data_ptr(), W, H, stream=stream)
                 hostframe.store(local.data_ptr(), stream)

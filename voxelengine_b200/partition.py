@@ -115,6 +115,17 @@ class FramePartition:
         return frame
 
 
+def _all_ok(err, world_size, group, what):
+    """Collective: raise on EVERY rank if `err` is set on any of them, so that the callers can fall back together."""
+    errs = [err]
+    if world_size > 1:
+        errs = [None] * world_size
+        dist.all_gather_object(errs, None if err is None else repr(err), group=group)
+    bad = [(r, e) for r, e in enumerate(errs) if e is not None]
+    if bad:
+        raise RuntimeError("%s failed on rank %d: %s" % (what, bad[0][0], bad[0][1]))
+
+
 class SharedFrame:
     """The frame of a multi-GPU partition, living in rank 0's HBM and mapped by every other rank (vx_shared_alloc /
     vx_shared_open, include/vxrt.h).  `ptr` is what each rank passes to render_device as d_bgra, with
@@ -135,8 +146,21 @@ class SharedFrame:
             box = [handle, my_gpu]
         if part.world_size > 1:
             dist.broadcast_object_list(box, src=0, group=group)
+        err = None
         if not self.owner:
-            self.ptr = vx.shared_open(box[0], device)
+            try:
+                self.ptr = vx.shared_open(box[0], device)
+            except Exception as e:  # e.g. no peer access between the two GPUs
+                self.ptr, err = None, e
+        try:
+            _all_ok(err, part.world_size, group, "mapping the shared frame")
+        except RuntimeError:
+            if self.owner:
+                vx.shared_free(self.ptr, device)
+            elif self.ptr is not None:
+                vx.shared_close(self.ptr, device)
+            self.ptr = None
+            raise
         self.remote = box[1] != my_gpu   # the frame is in another GPU's memory: this rank's pixel stores cross NVLink
         self._token = None
 
@@ -212,7 +236,22 @@ class HostFrame:
         os.close(fd)
         self._view = (ctypes.c_uint8 * self.nbytes).from_buffer(self._map)
         self.ptr = ctypes.addressof(self._view)
-        vx.host_register(self.ptr, self.nbytes)
+        err = None
+        try:
+            vx.host_register(self.ptr, self.nbytes)
+        except Exception as e:
+            err = e
+        try:
+            _all_ok(err, part.world_size, group, "page-locking the shared host frame")
+        except RuntimeError:
+            if err is None:
+                vx.host_unregister(self.ptr)
+            if part.rank == 0:
+                os.unlink(self.path)
+            self._view = None
+            self._map.close()
+            self._map = None
+            raise
         self.array = np.frombuffer(self._map, np.uint8, part.H * part.W * 4).reshape(part.H, part.W, 4)
         self._copy_stream = None
         if part.world_size > 1:
