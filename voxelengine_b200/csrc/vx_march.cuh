@@ -311,7 +311,11 @@ __device__ __forceinline__ void brick_done(const WorldView& w, Lane& L, const Fi
         lane_set_state(L, ST_DONE);
         return;
     }
-    V3 start = mk(fdiv(hit_pos.x, ff), fdiv(hit_pos.y, ff), fdiv(hit_pos.z, ff));
+    V3 start;
+    if ((w.factor & (w.factor - 1)) == 0) { // x / 2^k == x * 2^-k exactly (both are the correctly rounded value of the same number)
+        const float inv_f = fdiv(1.0f, ff);
+        start = mk(fmul(hit_pos.x, inv_f), fmul(hit_pos.y, inv_f), fmul(hit_pos.z, inv_f));
+    } else start = mk(fdiv(hit_pos.x, ff), fdiv(hit_pos.y, ff), fdiv(hit_pos.z, ff));
     if (q.oob && qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) { // :438-489
         start.x = nextafterf(start.x, L.d.x < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
         start.y = nextafterf(start.y, L.d.y < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
