@@ -315,8 +315,12 @@ __device__ __forceinline__ V3 sun_direction(const FrameParams& f, V3& once) {
     return normalize3<NORM>(once);
 }
 
-template <int NORM>
-__global__ void __launch_bounds__(256) shadow_setup(WorldView w, FrameParams f, ShadowQueue q) {
+#ifndef VX_SETUP_THREADS
+#define VX_SETUP_THREADS 256
+#define VX_SETUP_MIN_BLOCKS 4
+#endif
+template <int NORM, bool STATS>
+__global__ void __launch_bounds__(VX_SETUP_THREADS, VX_SETUP_MIN_BLOCKS) shadow_setup(WorldView w, FrameParams f, ShadowQueue q) {
     const unsigned long long n = *q.count;
     V3 sray;
     const V3 d = sun_direction<NORM>(f, sray);
@@ -326,11 +330,22 @@ __global__ void __launch_bounds__(256) shadow_setup(WorldView w, FrameParams f, 
         const V3 so = mk(fadd(r.x, fmul(sray.x, 0.01f)), fadd(r.y, fmul(sray.y, 0.01f)), fadd(r.z, fmul(sray.z, 0.01f)));
         Lane L;
         lane_setup(w, L, mk(fdiv(so.x, ff), fdiv(so.y, ff), fdiv(so.z, ff)), d, F_SHADOW);
-        L.tx = L.ty = L.tz = 0.0f; L.idx = 0;
+        L.tx = L.ty = L.tz = 0.0f; L.idx = 0; L.bidx = 0;
         lane_begin(w, L, kMaxSteps);
+        // A sun ray starts just off a surface, i.e. inside an occupied brick: its first examination finds that brick, and the
+        // march through it (a handful of voxel steps, much the same for the neighbouring pixels that sit next to each other
+        // in the queue) is done here, with all lanes busy, and so is the start of the traversal that follows.  shadow_rays
+        // picks the ray up from there.
+        if (lane_state(L) == ST_FAST && cell_bit(w.ptop, L.idx)) { L.bidx = L.idx; lane_set_state(L, ST_CAND); }
+        if (lane_state(L) == ST_CAND) {
+            V3 pos; uint32_t ncode;
+            lane_cand<false, STATS>(w, L, pos, ncode);
+            if (lane_state(L) == ST_BEGIN) lane_begin(w, L, kMaxSteps);
+        }
         q.lanes[3 * i] = make_uint4(__float_as_uint(L.s.x), __float_as_uint(L.s.y), __float_as_uint(L.s.z), __float_as_uint(L.tx));
-        q.lanes[3 * i + 1] = make_uint4(__float_as_uint(L.ty), __float_as_uint(L.tz), L.idx, 0u);
+        q.lanes[3 * i + 1] = make_uint4(__float_as_uint(L.ty), __float_as_uint(L.tz), L.idx, (uint32_t)L.total);
         q.lanes[3 * i + 2] = make_uint4(L.pc, L.flags, 0u, 0u);
+        if (STATS) { q.aux[i + 5 * f.ids] = L.work.C; q.aux[i + 6 * f.ids] = L.work.K; q.aux[i + 7 * f.ids] = L.work.E; }
     }
 }
 
@@ -371,8 +386,9 @@ struct ShadowPolicy {
         const uint4 a = q.lanes[3 * id], b = q.lanes[3 * id + 1], c = q.lanes[3 * id + 2];
         L.s = mk(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z));
         L.tx = __uint_as_float(a.w); L.ty = __uint_as_float(b.x); L.tz = __uint_as_float(b.y);
-        L.idx = b.z; L.total = 0; L.pc = c.x; L.flags = c.y;
+        L.idx = b.z; L.total = (int)b.w; L.pc = c.x; L.flags = c.y;
         L.csteps = 0; L.fsteps = 0; L.fcell = 0; L.work.C = L.work.K = L.work.E = 0;
+        if (STATS) { L.work.C = q.aux[id + 5 * f.ids]; L.work.K = q.aux[id + 6 * f.ids]; L.work.E = q.aux[id + 7 * f.ids]; } // shadow_setup's share
     }
 
     __device__ __forceinline__ void finish(const WorldView&, Lane& L, V3, uint32_t) {
@@ -762,7 +778,7 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
         } \
         VX_MARK(1); t->timed_kernels = 1; \
         if (shadow_pass && !t->primary_only) { \
-            shadow_setup<N><<<dense_blocks, 256, 0, cs>>>(w, f, q); \
+            shadow_setup<N, S><<<dense_blocks * (256 / VX_SETUP_THREADS), VX_SETUP_THREADS, 0, cs>>>(w, f, q); \
             VX_MARK(2); \
             if (!S && fuse) { \
                 rc = persistent_blocks(t, shadow_rays<N, false, true>, f.ids, blocks); if (rc) return rc; \
