@@ -77,6 +77,17 @@ __device__ __forceinline__ int steps_from_start(const Lane& L, int x, int y, int
     return abs(x - (int)L.s.x) + abs(y - (int)L.s.y) + abs(z - (int)L.s.z);
 }
 
+// p / factor (start = origin / factor, VolumeRaytracer.cu:361, and the re-seeding of :438).  For a power-of-two factor
+// x * (1 / factor) is the same float as x / factor — both are the correctly rounded value of the same real number.
+__device__ __forceinline__ V3 to_brick_units(const WorldView& w, V3 p) {
+    const float ff = (float)w.factor;
+    if ((w.factor & (w.factor - 1)) == 0) {
+        const float inv_f = fdiv(1.0f, ff);
+        return mk(fmul(p.x, inv_f), fmul(p.y, inv_f), fmul(p.z, inv_f));
+    }
+    return mk(fdiv(p.x, ff), fdiv(p.y, ff), fdiv(p.z, ff));
+}
+
 // Ray set-up shared by primary, shadow and batch rays: slab inverses, grid-entry clip (VolumeRaytracer.cu:361-381).
 // `s` is origin / factor, `d` the normalised direction.
 __device__ __forceinline__ void lane_setup(const WorldView& w, Lane& L, V3 s, V3 d, uint32_t keep_flags) {
@@ -311,11 +322,7 @@ __device__ __forceinline__ void brick_done(const WorldView& w, Lane& L, const Fi
         lane_set_state(L, ST_DONE);
         return;
     }
-    V3 start;
-    if ((w.factor & (w.factor - 1)) == 0) { // x / 2^k == x * 2^-k exactly (both are the correctly rounded value of the same number)
-        const float inv_f = fdiv(1.0f, ff);
-        start = mk(fmul(hit_pos.x, inv_f), fmul(hit_pos.y, inv_f), fmul(hit_pos.z, inv_f));
-    } else start = mk(fdiv(hit_pos.x, ff), fdiv(hit_pos.y, ff), fdiv(hit_pos.z, ff));
+    V3 start = to_brick_units(w, hit_pos);
     if (q.oob && qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) { // :438-489
         start.x = nextafterf(start.x, L.d.x < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
         start.y = nextafterf(start.y, L.d.y < 0.0f ? -CUDART_INF_F : CUDART_INF_F);

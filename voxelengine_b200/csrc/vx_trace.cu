@@ -47,7 +47,7 @@ struct BatchPolicy {
         const float ff = (float)w.factor;
         const V3 o = mk(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]);
         const V3 d = normalize3<NORM>(mk(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]));
-        lane_setup(w, L, mk(fdiv(o.x, ff), fdiv(o.y, ff), fdiv(o.z, ff)), d, 0u);
+        lane_setup(w, L, to_brick_units(w, o), d, 0u);
     }
     __device__ __forceinline__ void finish(const WorldView& w, Lane& L, V3 pos, uint32_t ncode) {
         const unsigned long long i = id;
@@ -277,7 +277,7 @@ struct PrimaryPolicy {
         pix = (uint32_t)x | ((uint32_t)y << 15) | ((f.crosshair && tx == (f.W >> 1) && ty == (f.H >> 1)) ? (1u << 30) : 0u);
         if (ORTHO) { // every ray runs along fwd (normalised by Raytrace only), from its own origin
             const V3 o = pixel_origin(f, true, x, y);
-            lane_setup(w, L, mk(fdiv(o.x, f.factor_f), fdiv(o.y, f.factor_f), fdiv(o.z, f.factor_f)), normalize3<NORM>(f.fwd), 0u);
+            lane_setup(w, L, to_brick_units(w, o), normalize3<NORM>(f.fwd), 0u);
             return;
         }
         // Raytrace normalises the (already normalised) direction it is given once more (VolumeRaytracer.cu:363)
@@ -329,7 +329,7 @@ __global__ void __launch_bounds__(VX_SETUP_THREADS, VX_SETUP_MIN_BLOCKS) shadow_
         const float4 r = q.rec[i];
         const V3 so = mk(fadd(r.x, fmul(sray.x, 0.01f)), fadd(r.y, fmul(sray.y, 0.01f)), fadd(r.z, fmul(sray.z, 0.01f)));
         Lane L;
-        lane_setup(w, L, mk(fdiv(so.x, ff), fdiv(so.y, ff), fdiv(so.z, ff)), d, F_SHADOW);
+        lane_setup(w, L, to_brick_units(w, so), d, F_SHADOW);
         L.tx = L.ty = L.tz = 0.0f; L.idx = 0; L.bidx = 0;
         lane_begin(w, L, kMaxSteps);
         // A sun ray starts just off a surface, i.e. inside an occupied brick: its first examination finds that brick, and the
