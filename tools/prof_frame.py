@@ -19,4 +19,14 @@ for _ in range(frames):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); rt.render_device(cam, vx.default_env(), opts, buf.data_ptr(), W, H, stream=torch.cuda.current_stream().cuda_stream); e1.record()
     torch.cuda.synchronize(); ts.append(e0.elapsed_time(e1))
-print(name, pos, "frame ms:", ["%.3f" % t for t in ts])
+import zlib
+crc = zlib.crc32(buf.cpu().numpy().tobytes())
+times = ""
+if os.environ.get("VX_KERNEL_TIMES"):  # per-kernel device times of a few more frames (events between the launches)
+    rt.set_timing(True)
+    acc = [0.0] * 4
+    for i in range(6):
+        rt.render_device(cam, vx.default_env(), opts, buf.data_ptr(), W, H, stream=torch.cuda.current_stream().cuda_stream)
+        acc = [a + b for a, b in zip(acc, rt.frame_times())]
+    times = " ".join("%s=%.3f" % (n, a / 6) for n, a in zip(rt.KERNELS, acc))
+print(name, pos, "frame ms:", ["%.3f" % t for t in ts], "crc32=%08x" % crc, times)

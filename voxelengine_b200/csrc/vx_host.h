@@ -102,5 +102,6 @@ struct vx_tracer {
     cudaStream_t copy_stream = nullptr; cudaEvent_t slice_ev[4] = {nullptr, nullptr, nullptr, nullptr}; // vx_render_host: copy/render overlap
     int fused_shade = 0;  // vx_tracer_set_fused_shade
     bool primary_only = false; unsigned long long* last_queue_count = nullptr; // vx_bounce_rays reuses vx_render's primary pass
+    cudaStream_t l2_stream = nullptr; const void* l2_base = nullptr; bool l2_tried = false; // pin_top_level (vx_trace.cu)
     bool timing = false; int timed_kernels = 0; cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // vx_tracer_set_timing
 };

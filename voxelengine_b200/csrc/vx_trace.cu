@@ -8,6 +8,9 @@
 #include "vx_march.cuh"
 #include <stdlib.h>
 
+#ifndef VX_TILE_SHAPE
+#define VX_TILE_SHAPE 0 // pixels a warp of primary_rays takes at a time: 0 = 8x4, 1 = 16x2, 2 = 32x1
+#endif
 #ifndef VX_TRACE_MIN_BLOCKS
 #define VX_TRACE_MIN_BLOCKS 8 // same for the batch kernel (it carries the parity planes' counters too)
 #endif
@@ -264,8 +267,19 @@ struct PrimaryPolicy {
         const uint32_t id = (uint32_t)id64;
         const uint32_t j = id & 31u, k = (id >> 5) & 3u, macro = id >> 7;
         const uint32_t lband = macro / f.mcols, mcol = macro - lband * f.mcols;
+#if VX_TILE_SHAPE == 0   // four 8x4 tiles per 16x8 macro tile
         const uint32_t tx = f.tx0 + mcol * 16u + (k & 1u) * 8u + (j & 7u);
         const uint32_t ty = f.ty0 + (lband * f.band_count + f.band_index) * 8u + (k >> 1) * 4u + (j >> 3);
+#elif VX_TILE_SHAPE == 1 // four 16x2 tiles per 16x8 macro tile
+        const uint32_t tx = f.tx0 + mcol * 16u + (j & 15u);
+        const uint32_t ty = f.ty0 + (lband * f.band_count + f.band_index) * 8u + k * 2u + (j >> 4);
+#elif VX_TILE_SHAPE == 3 // four 4x8 tiles per 16x8 macro tile
+        const uint32_t tx = f.tx0 + mcol * 16u + k * 4u + (j & 3u);
+        const uint32_t ty = f.ty0 + (lband * f.band_count + f.band_index) * 8u + (j >> 2);
+#else                    // four 32x1 tiles per 32x4 macro tile (mcols counts half-height macro tiles: two per 32 columns)
+        const uint32_t tx = f.tx0 + (mcol >> 1) * 32u + j;
+        const uint32_t ty = f.ty0 + (lband * f.band_count + f.band_index) * 8u + (mcol & 1u) * 4u + k;
+#endif
         if (tx >= f.tx0 + f.tw || ty >= f.ty0 + f.th) return;
         int x = (int)tx, y = (int)ty;
         if (f.checkerboard) { // Renderer.cu:186-194
@@ -571,6 +585,38 @@ static int next_counter(vx_tracer* t, cudaStream_t s, unsigned long long** out) 
     return VX_OK;
 }
 
+// The traversal grid (one occupancy bit per coarse cell, 8.7 MB at 8192x512x8192) is what every ray of every frame reads,
+// cell by cell; bricks and records are touched once or twice.  An access-policy window marks it persisting in L2 for the
+// kernels launched on `s`, so that the streaming traffic of a frame (records, brick masks, the frame queues, the pixels)
+// and whatever else runs between frames does not evict it.  Best effort: a device without persisting L2 just runs without.
+// VX_L2_PIN=0 switches it off.
+static void pin_top_level(vx_tracer* t, cudaStream_t s) {
+    static const bool enabled = [] { const char* e = getenv("VX_L2_PIN"); return !(e && atoi(e) == 0); }();
+    const vx_world* w = t->world;
+    if (!enabled || !w || !w->d_ptop) return;
+    if (t->l2_tried && t->l2_stream == s && t->l2_base == w->d_ptop) return;
+    t->l2_tried = true; t->l2_stream = s; t->l2_base = w->d_ptop;
+    const size_t pcells = (size_t)(w->cx + 2) * (w->cy + 2) * (w->cz + 2);
+    size_t bytes = (pcells + 31) / 32 * 4;
+    int max_window = 0, max_persist = 0;
+    cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, t->device);
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, t->device);
+    if (max_window <= 0 || max_persist <= 0) { cudaGetLastError(); return; }
+    if (bytes > (size_t)max_window) bytes = (size_t)max_window;
+    size_t carve = 0;
+    cudaDeviceGetLimit(&carve, cudaLimitPersistingL2CacheSize);
+    const size_t want = bytes < (size_t)max_persist ? bytes : (size_t)max_persist;
+    if (carve < want) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
+    cudaStreamAttrValue attr = {};
+    attr.accessPolicyWindow.base_ptr = (void*)w->d_ptop;
+    attr.accessPolicyWindow.num_bytes = bytes;
+    attr.accessPolicyWindow.hitRatio = want >= bytes ? 1.0f : (float)((double)want / (double)bytes);
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr);
+    cudaGetLastError(); // best effort
+}
+
 static int launch_trace(vx_tracer* t, const float* d_o, const float* d_d, size_t n, const vx_trace_opts* opts, const vx_hits* out,
                         cudaStream_t s) {
     if (n == 0) return VX_OK;
@@ -579,6 +625,7 @@ static int launch_trace(vx_tracer* t, const float* d_o, const float* d_d, size_t
     VX_REQUIRE(norm >= 0 && norm <= 2, "bad norm_mode");
     HitPlanes p{out->hit, out->pos, out->normal, out->steps, out->voxel, out->brick, out->coarse_steps, out->fine_steps, out->counters};
     const WorldView w = t->world->view();
+    pin_top_level(t, s);
     const bool count = out->counters != nullptr;
     unsigned long long* next = nullptr;
     int rc = next_counter(t, s, &next);
@@ -730,12 +777,17 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     const uint32_t bands = (f.th + 7u) / 8u;
     const uint32_t my_bands = bands > f.band_index ? (bands - f.band_index + f.band_count - 1u) / f.band_count : 0u;
     if (my_bands == 0) return VX_OK;
+#if VX_TILE_SHAPE == 2
+    f.mcols = (f.tw + 31u) / 32u * 2u;
+#else
     f.mcols = (f.tw + 15u) / 16u;
+#endif
     f.ids = (unsigned long long)f.mcols * my_bands * 128ull;
     VX_REQUIRE(f.ids < (1ull << 32), "frame too large for one launch");
     const WorldView w = t->world->view();
     unsigned long long* st = (unsigned long long*)opts->d_stats;
     cudaStream_t cs = (cudaStream_t)stream;
+    pin_top_level(t, cs);
     const bool shadow_pass = opts->shadows && !opts->debug_view;
     ShadowQueue q{nullptr, nullptr, nullptr, nullptr};
     if (shadow_pass) { // per-frame queue of primary hits waiting for their sun ray (one entry per pixel of this launch at most)
