@@ -436,6 +436,7 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 //   void finish(w, L, pos, ncode)         consume a finished march and set the lane ST_IDLE (or re-arm it)
 //   void flush()                          called by all 32 lanes whenever the whole warp is idle (before a refill / the end)
 //   kRefill                               idle lanes that trigger a refill (32: whole tiles only)
+//   kFastQuad, kLeaveNum, kLeaveDen       fast-loop scheduling, see lane_fast
 //   kDrain, void drain(uint32_t done)     kDrain: called by all 32 lanes once per round, after finish(), with the ballot of the
 //                                         lanes that finished this round (a policy batching its per-ray epilogue across the warp)
 // `next` is a zero-initialised device counter shared by all warps of the launch.
@@ -446,17 +447,37 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 #ifndef VX_FAST_CHUNK
 #define VX_FAST_CHUNK 64
 #endif
-#ifndef VX_LEAVE_NUM
-#define VX_LEAVE_NUM 1
-#define VX_LEAVE_DEN 4
+// Fast-loop scheduling, per ray source (Policy::kFastQuad, kLeaveNum / kLeaveDen): steps between looks at how many lanes are
+// still stepping, and the share of the lanes that entered below which the rest stop too.  Measured per 4K frame (profiles/):
+// primaries 4 steps, 1/4: 1.41 ms; 8 steps: 1.37 (1/4 and 1/2 alike); sun rays 4 steps, 1/4: 1.00 ms; 4 steps, 1/2: 0.95.
+#ifndef VX_PRIMARY_QUAD
+#define VX_PRIMARY_QUAD 8
 #endif
-constexpr int kFastQuad = 4;                // fast-loop steps between looks at how many lanes are still stepping
+#ifndef VX_PRIMARY_LEAVE_NUM
+#define VX_PRIMARY_LEAVE_NUM 1
+#define VX_PRIMARY_LEAVE_DEN 2
+#endif
+#ifndef VX_SHADOW_QUAD
+#define VX_SHADOW_QUAD 4
+#endif
+#ifndef VX_SHADOW_LEAVE_NUM
+#define VX_SHADOW_LEAVE_NUM 1
+#define VX_SHADOW_LEAVE_DEN 2
+#endif
+#ifndef VX_BATCH_QUAD
+#define VX_BATCH_QUAD 4
+#endif
+#ifndef VX_BATCH_LEAVE_NUM
+#define VX_BATCH_LEAVE_NUM 1
+#define VX_BATCH_LEAVE_DEN 4
+#endif
 constexpr int kChunk = 32;                  // ray ids a warp draws at a time (render: one 8x4 pixel tile)
 constexpr int kFastChunk = VX_FAST_CHUNK;   // coarse steps a lane may take before the warp looks at the other states again
 
 // ST_FAST: the hot loop over the bordered linear grid; leaving the grid shows up as an occupied (border) cell.
-template <bool COUNT>
+template <bool COUNT, int QUAD, int LEAVE_NUM, int LEAVE_DEN>
 __device__ __forceinline__ void lane_fast(const WorldView& w, Lane& L) {
+    static_assert(kFastChunk % QUAD == 0, "the step budget is counted in quads");
     const float dtx = lane_dt(L.d.x, L.ivx), dty = lane_dt(L.d.y, L.ivy), dtz = lane_dt(L.d.z, L.ivz);
     const int dix = L.d.x > 0.0f ? 1 : -1, diy = L.d.y > 0.0f ? w.pnx : -w.pnx, diz = L.d.z > 0.0f ? w.pnxy : -w.pnxy;
     float tx = L.tx, ty = L.ty, tz = L.tz;
@@ -464,20 +485,20 @@ __device__ __forceinline__ void lane_fast(const WorldView& w, Lane& L) {
     int budget = kFastChunk;
     // Lanes leave this loop one by one as they meet occupied cells.  Once most of the lanes that entered it are
     // waiting, the few still stepping stop too (they stay ST_FAST and go on in the next round): a warp serves
-    // its majority.  Checked every kFastQuad steps; a scheduling heuristic only, results do not depend on it.
+    // its majority.  Checked every QUAD steps; a scheduling heuristic only, results do not depend on it.
     const int entered = __popc(__activemask());
     bool found = false;
 #pragma unroll 1
     do {
 #pragma unroll
-        for (int k = 0; k < kFastQuad; ++k) {
+        for (int k = 0; k < QUAD; ++k) {
             if (cell_bit(w.ptop, idx)) { found = true; break; }
             if (COUNT) L.work.C++;
             fast_step(tx, ty, tz, idx, dtx, dty, dtz, dix, diy, diz);
         }
         if (found) { lane_set_state(L, ST_CAND); break; }
-        budget -= kFastQuad;
-    } while (budget > 0 && __popc(__activemask()) * VX_LEAVE_DEN >= entered * VX_LEAVE_NUM);
+        budget -= QUAD;
+    } while (budget > 0 && __popc(__activemask()) * LEAVE_DEN >= entered * LEAVE_NUM);
     L.tx = tx; L.ty = ty; L.tz = tz; L.idx = idx; L.bidx = idx;
 }
 
@@ -498,7 +519,7 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
         V3 pos = mk(0.0f, 0.0f, 0.0f);
         uint32_t ncode = 0;
         if (lane_state(L) == ST_BEGIN) lane_begin(w, L, max_steps);
-        if (lane_state(L) == ST_FAST) lane_fast<COUNT>(w, L);
+        if (lane_state(L) == ST_FAST) lane_fast<COUNT, Policy::kFastQuad, Policy::kLeaveNum, Policy::kLeaveDen>(w, L);
         if (lane_state(L) == ST_SLOW) lane_slow<COUNT>(w, L);
         if (lane_state(L) == ST_CAND) lane_cand<BATCH, COUNT>(w, L, pos, ncode);
         if constexpr (Policy::kDrain) {

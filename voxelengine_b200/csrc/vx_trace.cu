@@ -40,6 +40,7 @@ struct BatchPolicy {
     unsigned long long id; // per lane: the ray being marched
     static constexpr int kRefill = VX_REFILL_MIN;
     static constexpr bool kDrain = false;
+    static constexpr int kFastQuad = VX_BATCH_QUAD, kLeaveNum = VX_BATCH_LEAVE_NUM, kLeaveDen = VX_BATCH_LEAVE_DEN;
 
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return cap; }
@@ -213,6 +214,7 @@ __device__ __forceinline__ void emit_pixel(const FrameParams& f, bool ortho, uin
 template <int NORM, bool STATS, bool ORTHO>
 struct PrimaryPolicy {
     static constexpr bool kDrain = false;
+    static constexpr int kFastQuad = VX_PRIMARY_QUAD, kLeaveNum = VX_PRIMARY_LEAVE_NUM, kLeaveDen = VX_PRIMARY_LEAVE_DEN;
     static constexpr int kRefill = 32; // a warp takes a whole tile at a time: neighbouring rays stay in step (2.2 ms instead of
                                        // 1.56 ms per 4K frame with 16..28), and flush() relies on it
 #ifndef VX_SHADOW_REFILL
@@ -375,6 +377,7 @@ template <int NORM, bool STATS, bool FUSE>
 struct ShadowPolicy {
     static constexpr int kRefill = VX_SHADOW_REFILL;
     static constexpr bool kDrain = FUSE;
+    static constexpr int kFastQuad = VX_SHADOW_QUAD, kLeaveNum = VX_SHADOW_LEAVE_NUM, kLeaveDen = VX_SHADOW_LEAVE_DEN;
     const FrameParams& f;
     ShadowQueue q;
     uint8_t* __restrict__ bgra;
