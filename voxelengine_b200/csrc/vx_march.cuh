@@ -449,7 +449,8 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 #endif
 // Fast-loop scheduling, per ray source (Policy::kFastQuad, kLeaveNum / kLeaveDen): steps between looks at how many lanes are
 // still stepping, and the share of the lanes that entered below which the rest stop too.  Measured per 4K frame (profiles/):
-// primaries 4 steps, 1/4: 1.41 ms; 8 steps: 1.37 (1/4 and 1/2 alike); sun rays 4 steps, 1/4: 1.00 ms; 4 steps, 1/2: 0.95.
+// primaries 4 steps, 1/4: 1.41 ms; 8 steps: 1.37 (1/4 and 1/2 alike); sun rays 4 steps, 1/4: 1.00 ms; 4 steps, 1/2: 0.95-0.96;
+// incoherent bounce rays (batch kernel) 4 steps, 1/4: 2.30 ms; 8 steps: 2.25; 1/2: 2.46.
 #ifndef VX_PRIMARY_QUAD
 #define VX_PRIMARY_QUAD 8
 #endif
@@ -465,7 +466,7 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 #define VX_SHADOW_LEAVE_DEN 2
 #endif
 #ifndef VX_BATCH_QUAD
-#define VX_BATCH_QUAD 4
+#define VX_BATCH_QUAD 8
 #endif
 #ifndef VX_BATCH_LEAVE_NUM
 #define VX_BATCH_LEAVE_NUM 1
