@@ -77,13 +77,17 @@ class ClockSampler:
             mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
 
             def loop():
-                while not self.halt:
+                failures = 0
+                while not self.halt and failures < 1000:
                     try:
                         self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
                         self.mx.append(mx)
+                    except Exception:
+                        failures += 1
+                    try:
                         self.bits |= int(reasons(h))
                     except Exception:
-                        break
+                        failures += 1
                     time.sleep(0.002)
             self.thread = threading.Thread(target=loop, daemon=True)
             self.thread.start()
