@@ -148,12 +148,14 @@ __device__ __forceinline__ V3 shade(const FrameParams& f, V3 cam, V3 n, V3 pos, 
     return mk(fdiv(c.x, fadd(c.x, 1.0f)), fdiv(c.y, fadd(c.y, 1.0f)), fdiv(c.z, fadd(c.z, 1.0f)));
 }
 
-// A frame is two launches:
+// A shadowed frame is four launches:
 //   primary_rays : persistent warps, one 8x4 pixel tile per refill (coherent rays).  A miss writes its pixel; a hit
 //                  is either shaded at once (shadows off / debug view) or appended to the frame's shadow queue.
-//   shadow_rays  : persistent warps pull queue entries (neighbouring pixels sit next to each other in the queue) and
+//   shadow_setup : dense, one thread per queued hit: the sun ray's set-up, its first brick and the traversal start after it.
+//   shadow_rays  : persistent warps pull the lane records (neighbouring pixels sit next to each other in the queue) and
 //                  refill finished lanes in groups, because about half of the sun rays end after a few steps while
-//                  the rest cross the whole grid; the pixel is shaded and written when its shadow ray ends.
+//                  the rest cross the whole grid.
+//   shade_pixels : dense: entry + result -> pixel (or, FUSE, inside shadow_rays for a frame in another GPU's memory).
 // Ray id -> pixel for the primary launch: ids are dealt in 8x4 tiles (32 consecutive ids), four tiles forming a
 // 16x8 macro tile, macro tiles row-major inside this launch's bands.  Pixel (thread) coordinates and the written
 // image are the reference's.
