@@ -78,6 +78,7 @@ typedef struct vx_world_info {
     uint64_t solid_voxels;
     uint64_t bytes_top, bytes_records, bytes_pool;
     float build_ms;           /* device time of the last build (CUDA events) */
+    float tiles_ms;           /* of which: the voxel kernel (noise_tiles, the PopulateVoxels replacement; dense_tiles for a given grid) */
 } vx_world_info;
 int vx_world_get_info(const vx_world* w, vx_world_info* info);
 
@@ -85,6 +86,12 @@ int vx_world_get_info(const vx_world* w, vx_world_info* info);
  * words), per-brick masks indexed by coarse tiled index (bricks * factor^3/32 words, zeros for
  * empty bricks) and per-brick bounds (bricks * 6 floats: min xyz, max xyz; 0,0,0,-1,-1,-1 when
  * empty) — exactly what GenerateLowresVoxelBuffer returns.  Any pointer may be NULL. */
+int vx_world_download(const vx_world* w, uint32_t* top_words, uint32_t* brick_words, float* bounds6);
+/* The same export for n bricks picked by coarse coordinates (host array of n*3 uint32): occupied[i] bit 0 = the traversal
+ * grid's top-level bit, bit 1 = the reference-indexed top-level bit (they must agree); masks and bounds as above, n
+ * entries each.  For parity spot checks of worlds too large to export whole (8192x512x8192 is 5.5 GB in reference form). */
+int vx_world_download_bricks(const vx_world* w, const uint32_t* coarse_xyz, size_t n, uint8_t* occupied, uint32_t* brick_words,
+                             float* bounds6);
 /* Editing and storing a built world (the reference README's "modifiable terrain" / streaming items; the
  * reference can only flip bits of the dense grid through BitRef::operator=, VolumeRaytracer.cu:19-36, and rebuild).
  * vx_world_edit sets (solid != 0) or clears the n voxels voxels_xyz[3*i..] (host array; coordinates outside the world
@@ -96,7 +103,6 @@ int vx_world_get_info(const vx_world* w, vx_world_info* info);
 int vx_world_edit(vx_world* w, const uint32_t* voxels_xyz, size_t n, int solid);
 int vx_world_save(const vx_world* w, const char* path);
 int vx_world_load(vx_world** out, const char* path, int device);
-int vx_world_download(const vx_world* w, uint32_t* top_words, uint32_t* brick_words, float* bounds6);
 
 /* ------------------------------------------------------------------------------------------
  * Tracer.  Replaces VoxelRaytracer3D(size_t count) / ~VoxelRaytracer3D  VolumeRaytracer.cuh:318-334
@@ -167,7 +173,10 @@ typedef struct vx_render_opts {
 
 void vx_get_directions(const float euler_xyz[3], float fwd[3], float up[3], float right[3]); /* Renderer.cu:27-42 */
 /* d_bgra: W*H*4 bytes of device memory, BGRA8888 (Renderer.cuh:29-31); asynchronous on `stream`.
- * d_steps (optional, W*H int32): per-pixel step count incl. shadow steps. */
+ * d_steps (optional, W*H int32): per-pixel step count incl. shadow steps.
+ * ONE FRAME IN FLIGHT PER TRACER: a tracer owns the frame's hit queue, ray counters and timing events, so consecutive
+ * vx_render / vx_bounce_rays / vx_trace_device calls on the same tracer must go to the same stream (or be separated by a
+ * synchronisation); use one tracer per stream to overlap frames (tracers share the world, which is read-only). */
 int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* opts,
               void* d_bgra, int32_t* d_steps, uint32_t W, uint32_t H, void* stream);
 /* Same into host memory (render into the tracer's device frame, then D2H; synchronous): the
@@ -210,11 +219,15 @@ int vx_shared_open(const uint8_t handle[VX_SHARED_HANDLE_BYTES], int device, voi
 int vx_shared_close(void* d_ptr, int device); /* a pointer from vx_shared_open */
 int vx_shared_free(void* d_ptr, int device);  /* a pointer from vx_shared_alloc */
 int vx_device_to_host(void* h_dst, const void* d_src, size_t bytes, int device, void* stream);
+int vx_device_fill(void* d_dst, int byte, size_t bytes, int device, void* stream); /* cudaMemset on any device pointer; waits */
 /* The frame for a consumer on the host (main.cu:165-167 copies it down every frame) when several ranks render it: one
  * host frame of W*H*4 bytes in memory all the ranks' processes map (POSIX shared memory), page-locked in each process
  * by vx_host_register; after vx_render with band_count / band_index into its own device frame, each rank's
  * vx_bands_to_host enqueues the copy of exactly its 8-row bands into their places of the host frame on `stream` —
- * every rank down its own PCIe link, no GPU-to-GPU exchange.  The caller synchronises the streams and the ranks. */
+ * every rank down its own PCIe link, no GPU-to-GPU exchange.  The caller synchronises the streams and the ranks.
+ * NOT for checkerboard frames: vx_render deals bands of 8 THREAD rows, and with checkerboard = 1 thread row ty writes
+ * pixel rows 2 ty .. 2 ty + 2, so neighbouring bands interleave in pixel space and no row copy separates them.  Render
+ * such partitions into one shared frame (vx_shared_alloc / vx_shared_open), where every pixel is stored by its owner. */
 int vx_host_register(void* h_ptr, size_t bytes);
 int vx_host_unregister(void* h_ptr);
 int vx_bands_to_host(void* h_frame, const void* d_frame, uint32_t W, uint32_t H, uint32_t band_count, uint32_t band_index,

@@ -7,7 +7,10 @@
  *   build  X Y Z factor out.bin                      dump GenerateLowresVoxelBuffer(CreateVoxels(..))
  *   trace  X Y Z factor rays.bin out.bin             VoxelRaytracer3D::Raytrace on rays.bin (n, origins, dirs)
  *   render X Y Z factor W H px py pz ex ey ez frames out.bgra [ow oh]   Graphics::RenderScreen, `frames` times
- *                                                              (ow oh: SetOrthoWindowSize, used by the -DORTHO build)
+ *                                                              (ow oh: SetOrthoWindowSize, used by the -DORTHO build);
+ *                                                              out.bgra = the buffer after frame 0; with VXREF_DUMP_LAST=path
+ *                                                              the buffer after the last frame goes to `path` (the checkerboard
+ *                                                              halves of consecutive frames fill it, main.cu:165-167)
  * Timings are printed as "key=value" lines.
  */
 #include "VolumeRaytracer.cuh"
@@ -132,6 +135,12 @@ int main(int argc, char** argv) {
         FILE* g = fopen(argv[15], "wb");
         fwrite(first.data(), 1, first.size(), g); // frame 0 alone (FrameNumber 0 during the launch)
         fclose(g);
+        if (const char* last = getenv("VXREF_DUMP_LAST")) {
+            cudaMemcpy(first.data(), d_pixels, first.size(), cudaMemcpyDeviceToHost);
+            FILE* l = fopen(last, "wb");
+            fwrite(first.data(), 1, first.size(), l);
+            fclose(l);
+        }
         return 0;
     }
     fprintf(stderr, "unknown command %s\n", cmd);

@@ -5,6 +5,7 @@
  * (VolumeRaytracer.cu:354), DDARayTraversal (:176) and RayIntersectsAABB (:124) as they are.
  */
 #include "VolumeRaytracer.cuh"
+#include "helper_math.h"
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -31,6 +32,44 @@ extern "C" vxref_world* vxref_build(const uint32_t* bits, uint32_t X, uint32_t Y
     w->nbricks = (size_t)w->top.dimensions[0] * w->top.dimensions[1] * w->top.dimensions[2];
     return w;
 }
+/* A reference-form world assembled from brickmap arrays the caller keeps alive (top-level bits in the tiled index, factor^3/32
+ * words per brick in tiled coarse order, six floats of bounds per brick): what GenerateLowresVoxelBuffer returns, without the
+ * dense grid it needs as input — 2^35 voxels at 8192x512x8192, beyond the reference's 32-bit voxel index.  Raytrace itself only
+ * indexes the coarse grid and single bricks, so the reference's own march runs on such a world unchanged.  BitArray keeps its
+ * two fields private (VolumeRaytracer.cuh:204-223: size_t size; uint32_t* data), hence the layout-checked memcpy. */
+struct RawBits { size_t size; uint32_t* data; };
+static_assert(sizeof(RawBits) == sizeof(BitArray), "BitArray layout");
+static void adopt(BitArray& dst, size_t bits, const uint32_t* words) {
+    RawBits r{bits, const_cast<uint32_t*>(words)};
+    std::memcpy((void*)&dst, &r, sizeof r);
+}
+extern "C" vxref_world* vxref_from_brickmap(const uint32_t* top_words, const uint32_t* brick_words, const float* bounds6,
+                                            uint32_t X, uint32_t Y, uint32_t Z, int factor) {
+    static_assert(sizeof(Bounds3Df) == 24, "Bounds3Df layout");
+    vxref_world* w = new vxref_world();
+    const uint32_t cx = X / factor, cy = Y / factor, cz = Z / factor;
+    w->factor = factor;
+    w->nbricks = (size_t)cx * cy * cz;
+    adopt(w->top.grid, w->nbricks, top_words);
+    w->top.dimensions[0] = (uint16_t)cx; w->top.dimensions[1] = (uint16_t)cy; w->top.dimensions[2] = (uint16_t)cz;
+    const size_t bits = (size_t)factor * factor * factor, wpb = bits / 32;
+    w->bricks = new VoxelBuffer3D[w->nbricks];
+    w->bounds = reinterpret_cast<Bounds3Df*>(const_cast<float*>(bounds6));
+    for (size_t i = 0; i < w->nbricks; ++i) {
+        const bool occupied = (top_words[i >> 5] >> (i & 31)) & 1u;
+        if (!occupied) continue; /* empty brick: dimensions 0, no grid (VolumeRaytracer.cuh:379-516) */
+        adopt(w->bricks[i].grid, bits, brick_words + i * wpb);
+        w->bricks[i].dimensions[0] = w->bricks[i].dimensions[1] = w->bricks[i].dimensions[2] = (uint16_t)factor;
+    }
+    return w;
+}
+extern "C" void vxref_free_view(vxref_world* w) { if (w) { delete[] w->bricks; delete w; } }
+/* helper_math.h normalize (:1325-1329, host rsqrtf here) and reflect (:1427-1430) as the reference's AO sample loop uses them */
+extern "C" void vxref_normalize(const float* v, float* out) { float3 r = normalize(make_float3(v[0], v[1], v[2])); out[0] = r.x; out[1] = r.y; out[2] = r.z; }
+extern "C" void vxref_reflect(const float* i, const float* n, float* out) {
+    float3 r = reflect(make_float3(i[0], i[1], i[2]), make_float3(n[0], n[1], n[2])); out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+extern "C" float vxref_dot(const float* a, const float* b) { return dot(make_float3(a[0], a[1], a[2]), make_float3(b[0], b[1], b[2])); }
 extern "C" void vxref_export(vxref_world* w, uint32_t* top_words, uint32_t* brick_words, float* bounds6) {
     size_t wpb = (size_t)w->factor * w->factor * w->factor / 32;
     std::memcpy(top_words, w->top.grid.Raw(), (w->nbricks + 31) / 32 * 4);

@@ -113,6 +113,15 @@ void vxo_render_sample(const vxo_world* w, const vxo_camera* cam, const vxo_env*
                        uint32_t W, uint32_t H, uint32_t ty_begin, uint32_t ty_end, uint32_t ty_stride,
                        uint8_t* bgra, uint64_t* stats_out, int nthreads);
 
+/* the same sample with its pixels (W*H*4 bytes, unsampled rows untouched) and step plane (W*H int32) written */
+void vxo_render_sample_planes(const vxo_world* w, const vxo_camera* cam, const vxo_env* env, const vxo_render_opts* o,
+                              uint32_t W, uint32_t H, uint32_t ty_begin, uint32_t ty_end, uint32_t ty_stride,
+                              uint8_t* bgra, int32_t* steps_plane, int nthreads);
+/* the rays screenDispatch gives Raytrace on those rows (primary rays, and a sun ray per primary hit), as a batch */
+size_t vxo_frame_rays(const vxo_world* w, const vxo_camera* cam, const vxo_env* env, const vxo_render_opts* o,
+                      uint32_t W, uint32_t H, uint32_t ty_begin, uint32_t ty_end, uint32_t ty_stride,
+                      float* origins, float* dirs, size_t capacity);
+
 #ifdef __cplusplus
 }
 #endif

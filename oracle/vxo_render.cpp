@@ -188,6 +188,75 @@ extern "C" void vxo_render(const vxo_world* w, const vxo_camera* cam, const vxo_
     });
 }
 
+/* vxo_render_sample with the two planes a parity check needs: pixels of the sampled thread rows are written to bgra (W*H*4
+ * bytes, others untouched) and their step counts (primary + sun-ray DDA steps) to steps_plane (W*H int32). */
+extern "C" void vxo_render_sample_planes(const vxo_world* w, const vxo_camera* cam, const vxo_env* env, const vxo_render_opts* o,
+                                         uint32_t W, uint32_t H, uint32_t ty_begin, uint32_t ty_end, uint32_t ty_stride,
+                                         uint8_t* bgra, int32_t* steps_plane, int nthreads) {
+    Frame f{w, cam, env, o, W, H, bgra, steps_plane, 0.0f};
+    if (cam->tan_half > 0.0f) f.tan_half = cam->tan_half;
+    else {
+        const float fov = (float)((double)cam->fov_deg * 3.1415 / 180.0);
+        f.tan_half = std::tan(fov / 2.0f);
+    }
+    const uint32_t rows = o->checkerboard ? (H >> 1) : H;
+    if (ty_end > rows) ty_end = rows;
+    if (ty_stride == 0) ty_stride = 1;
+    const uint32_t cols = (W + 31) / 32 * 32;
+    const size_t nrows = ty_end > ty_begin ? (ty_end - ty_begin + ty_stride - 1) / ty_stride : 0;
+    parallel_for(nrows, nthreads, [&](size_t lo, size_t hi) {
+        for (size_t r = lo; r < hi; ++r)
+            for (uint32_t tx = 0; tx < cols; ++tx) pixel(f, (int)tx, (int)(ty_begin + r * ty_stride));
+    });
+}
+
+/* The rays screenDispatch hands to Raytrace for the sampled thread rows, as a flat list for a batch tracer (bench.py's
+ * reference arm feeds them to the reference's own Raytrace compiled for the host): every pixel's primary ray
+ * (Renderer.cu:199-211) and, for every primary hit, calculateColor's shadow ray (:98-102).  origins/dirs hold up to
+ * `capacity` rays of 3 floats; returns the number of rays (which may exceed capacity: nothing is written past it). */
+extern "C" size_t vxo_frame_rays(const vxo_world* w, const vxo_camera* cam, const vxo_env* env, const vxo_render_opts* o,
+                                 uint32_t W, uint32_t H, uint32_t ty_begin, uint32_t ty_end, uint32_t ty_stride,
+                                 float* origins, float* dirs, size_t capacity) {
+    Frame f{w, cam, env, o, W, H, nullptr, nullptr, 0.0f};
+    if (cam->tan_half > 0.0f) f.tan_half = cam->tan_half;
+    else {
+        const float fov = (float)((double)cam->fov_deg * 3.1415 / 180.0);
+        f.tan_half = std::tan(fov / 2.0f);
+    }
+    const uint32_t rows = o->checkerboard ? (H >> 1) : H;
+    if (ty_end > rows) ty_end = rows;
+    if (ty_stride == 0) ty_stride = 1;
+    const uint32_t cols = (W + 31) / 32 * 32;
+    const V3 L{env->light_dir[0], env->light_dir[1], env->light_dir[2]};
+    const V3 sray = norm3(L, o->norm_mode);
+    const size_t nrows = ty_end > ty_begin ? (ty_end - ty_begin + ty_stride - 1) / ty_stride : 0;
+    std::vector<std::vector<float>> per_row(nrows); /* 6 floats per ray, rows marched in parallel, order kept */
+    parallel_for(nrows, 0, [&](size_t lo, size_t hi) {
+        for (size_t r = lo; r < hi; ++r) {
+            std::vector<float>& out = per_row[r];
+            const uint32_t ty = ty_begin + (uint32_t)r * ty_stride;
+            for (uint32_t tx = 0; tx < cols; ++tx) {
+                int x = (int)tx, y = (int)ty;
+                if (o->checkerboard) { y *= 2; if ((x % 2) == 0) y += 1; if (o->frame_number % 2 == 0) y += 1; }
+                if ((uint32_t)x >= W || (uint32_t)y >= H) continue;
+                const bool orth = ortho(f);
+                const V3 origin = orth ? ortho_origin(f, x, y) : V3{cam->origin[0], cam->origin[1], cam->origin[2]};
+                const V3 rd = orth ? V3{cam->fwd[0], cam->fwd[1], cam->fwd[2]} : primary_dir(f, x, y);
+                out.insert(out.end(), {origin.x, origin.y, origin.z, rd.x, rd.y, rd.z});
+                if (o->debug_view || !o->shadows) continue;
+                MarchOut m;
+                if (march(*w, origin, rd, o->norm_mode, kMaxSteps, m))
+                    out.insert(out.end(), {m.pos.x + sray.x * 0.01f, m.pos.y + sray.y * 0.01f, m.pos.z + sray.z * 0.01f, sray.x, sray.y, sray.z});
+            }
+        }
+    });
+    size_t n = 0;
+    for (const auto& row : per_row)
+        for (size_t k = 0; k + 5 < row.size(); k += 6, ++n)
+            if (n < capacity) { std::memcpy(origins + 3 * n, &row[k], 12); std::memcpy(dirs + 3 * n, &row[k + 3], 12); }
+    return n;
+}
+
 /* A bounded sample of a frame for the timed CPU baseline: thread rows ty_begin, ty_begin+ty_stride, ...
  * < ty_end (clamped to the frame's grid).  bgra may be NULL (nothing is stored).  stats_out[8] receives
  * primary rays, primary hits, shadow rays, shadow hits, steps, C, K, E of the sample. */

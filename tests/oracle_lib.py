@@ -87,6 +87,12 @@ def lib():
         L.vxo_render_sample.restype = None
         L.vxo_render_sample.argtypes = [C.c_void_p, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts), C.c_uint32,
                                         C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
+        L.vxo_render_sample_planes.restype = None
+        L.vxo_render_sample_planes.argtypes = [C.c_void_p, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts), C.c_uint32,
+                                               C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
+        L.vxo_frame_rays.restype = C.c_size_t
+        L.vxo_frame_rays.argtypes = [C.c_void_p, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts), C.c_uint32,
+                                     C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_size_t]
         L.vxo_world_from_brickmap_view.restype = C.c_void_p
         L.vxo_world_from_brickmap_view.argtypes = [_u32p, _u32p, _f32p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int]
         _lib = L
@@ -135,6 +141,23 @@ class OracleWorld:
         lib().vxo_render_sample(self.h, C.byref(cam), C.byref(env), C.byref(opts), W, H, ty_begin, ty_end, ty_stride,
                                 None, stats.ctypes.data, nthreads)
         return stats
+
+    def render_sample_planes(self, cam, env, opts, W, H, ty_begin, ty_end, ty_stride, bgra, steps, nthreads=0):
+        """The sampled thread rows' pixels into bgra (H x W x 4 uint8) and step counts into steps (H x W int32)."""
+        assert bgra.dtype == np.uint8 and bgra.size == W * H * 4 and steps.dtype == np.int32 and steps.size == W * H
+        lib().vxo_render_sample_planes(self.h, C.byref(cam), C.byref(env), C.byref(opts), W, H, ty_begin, ty_end, ty_stride,
+                                       bgra.ctypes.data, steps.ctypes.data, nthreads)
+
+    def frame_rays(self, cam, env, opts, W, H, ty_begin, ty_end, ty_stride):
+        """(origins, dirs) screenDispatch hands to Raytrace on the sampled rows: primaries + one sun ray per primary hit."""
+        rows = len(range(ty_begin, min(ty_end, H), max(ty_stride, 1)))
+        cap = rows * ((W + 31) // 32 * 32) * 2
+        o = np.zeros((cap, 3), np.float32)
+        d = np.zeros((cap, 3), np.float32)
+        n = lib().vxo_frame_rays(self.h, C.byref(cam), C.byref(env), C.byref(opts), W, H, ty_begin, ty_end, ty_stride,
+                                 o.ctypes.data, d.ctypes.data, cap)
+        assert n <= cap
+        return o[:n], d[:n]
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -240,7 +263,42 @@ def ref_host():
     L.vxref_ray_aabb.argtypes = [_f32p] * 6
     L.vxref_sample_index.restype = C.c_uint32
     L.vxref_sample_index.argtypes = [C.c_uint32] * 5
+    if hasattr(L, "vxref_from_brickmap"):
+        L.vxref_from_brickmap.restype = C.c_void_p
+        L.vxref_from_brickmap.argtypes = [_u32p, _u32p, _f32p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int]
+        L.vxref_free_view.argtypes = [C.c_void_p]
+        L.vxref_normalize.argtypes = [_f32p, _f32p]
+        L.vxref_reflect.argtypes = [_f32p, _f32p, _f32p]
+        L.vxref_dot.restype = C.c_float
+        L.vxref_dot.argtypes = [_f32p, _f32p]
     return L
+
+
+class RefWorld:
+    """The reference's own march (GPUDDA::Raytrace compiled for the host, oracle/_ref/libvxref_host.so) on a brickmap in
+    the reference's form that the caller keeps alive (e.g. vx.World.download())."""
+
+    def __init__(self, top, brick_bits, bounds, X, Y, Z, factor=8):
+        self.L = ref_host()
+        if self.L is None or not hasattr(self.L, "vxref_from_brickmap"):
+            raise RuntimeError("oracle/_ref/libvxref_host.so not built")
+        self._keep = (np.ascontiguousarray(top, np.uint32), np.ascontiguousarray(brick_bits, np.uint32),
+                      np.ascontiguousarray(bounds, np.float32).reshape(-1))
+        self.h = self.L.vxref_from_brickmap(*self._keep, X, Y, Z, factor)
+
+    def trace(self, origins, dirs, max_steps=2048, nthreads=0):
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        n = o.shape[0]
+        hit, steps = np.zeros(n, np.uint8), np.zeros(n, np.int32)
+        pos, nrm = np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+        self.L.vxref_trace(self.h, o, d, n, max_steps, hit.ctypes.data, pos, nrm, steps.ctypes.data, nthreads)
+        return dict(hit=hit, pos=pos, normal=nrm, steps=steps)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.vxref_free_view(self.h)
+            self.h = None
 
 
 def ref_noise():

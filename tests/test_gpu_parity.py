@@ -289,24 +289,7 @@ def test_bands_and_tiles_compose_the_full_frame(vx, gpu_worlds):
     rt.close()
 
 
-def _host_normalize(v):
-    """normalize() with CUDA's host rsqrtf: (float)(1.0 / sqrt((double)dot)), dot in float32 left to right."""
-    v = v.astype(np.float32)
-    d = (v[:, 0] * v[:, 0] + v[:, 1] * v[:, 1]).astype(np.float32) + (v[:, 2] * v[:, 2]).astype(np.float32)
-    inv = (1.0 / np.sqrt(d.astype(np.float64))).astype(np.float32)
-    return (v * inv[:, None]).astype(np.float32)
-
-
-def _noise_hash(seed):
-    s = seed.astype(np.uint32)
-    with np.errstate(over="ignore"):
-        s = (s + np.uint32(0x7ed55d16)) + (s << np.uint32(12))
-        s = (s ^ np.uint32(0xc761c23c)) ^ (s >> np.uint32(19))
-        s = (s + np.uint32(0x165667b1)) + (s << np.uint32(5))
-        s = (s + np.uint32(0xd3a2646c)) ^ (s << np.uint32(9))
-        s = (s + np.uint32(0xfd7046c5)) + (s << np.uint32(3))
-        s = (s ^ np.uint32(0xb55a4f09)) ^ (s >> np.uint32(16))
-    return s
+from bounce_ref import host_normalize as _host_normalize, noise_hash as _noise_hash, sample_rays  # noqa: E402
 
 
 @pytest.mark.parametrize("checkerboard,frame", [(0, 0), (1, 3)])
@@ -352,18 +335,7 @@ def test_bounce_rays_match_reference_sample_loop(vx, gpu_worlds, checkerboard, f
     sel = np.nonzero(rendered & prim["hit"].astype(bool))[0]
     assert np.array_equal(sel, pix), "bounce rays must exist exactly for the rendered primary hits"
     nrm = (-prim["normal"][sel]).astype(np.float32)
-    with np.errstate(over="ignore"):
-        si = (tys[sel] * W + xs[sel] + (frame + 1) * 1000).astype(np.int32)
-        r = [(_noise_hash((si * np.int32(k)).astype(np.int32).view(np.uint32)).astype(np.float32) / np.float32(0xffffffff)) for k in (1, 10, 100)]
-    sd = _host_normalize(np.stack([v * np.float32(2) - np.float32(1) for v in r], 1))
-
-    def dot(a, b):
-        return ((a[:, 0] * b[:, 0] + a[:, 1] * b[:, 1]).astype(np.float32) + a[:, 2] * b[:, 2]).astype(np.float32)
-    flip = dot(sd, nrm) < 0
-    dn = dot(nrm, sd)
-    refl = (sd - ((np.float32(2) * nrm).astype(np.float32) * dn[:, None]).astype(np.float32)).astype(np.float32)
-    sd = np.where(flip[:, None], refl, sd)
-    eo = (prim["pos"][sel] + (nrm * np.float32(0.01)).astype(np.float32)).astype(np.float32)
+    eo, sd = sample_rays(xs[sel], tys[sel], W, frame, prim["pos"][sel], nrm)
     assert np.array_equal(bd.view(np.uint32), sd.view(np.uint32)), "sample directions differ"
     assert np.array_equal(bo.view(np.uint32), eo.view(np.uint32)), "sample origins differ"
 
@@ -393,3 +365,29 @@ def test_render_host_sliced_path_equals_device_render(vx, gpu_worlds):
         got = rt.render_host(cam, vx.default_env(), opts, W, H, bgra=np.full((H, W, 4), 7, np.uint8))
         assert np.array_equal(got, frame.cpu().numpy())
         rt.close()
+
+
+def test_batch_call_pipeline_planes_and_ragged_chunks(vx, gpu_worlds):
+    """vx_trace with host arrays runs as a pipeline over 256 Ki-ray chunks through a page-locked ring: a batch that is not
+    a whole number of chunks, every plane and subsets of planes, must equal the device-pointer call and the oracle."""
+    import torch
+    dims, org = (128, 64, 128), (512, 0, 256)
+    w = gpu_worlds(dims, org, 8)
+    ow = worlds.oracle_world(dims, org, 8)
+    n = 3 * 256 * 1024 + 12345   # four chunks, the last one ragged; more chunks than ring slots
+    o, d = mixed_rays(dims, n, seed=4242)
+    rt = vx.VoxelRaytracer3D(w, n)
+    full = rt.raytrace(o, d, norm_mode=vx.NORM_HOST, counters=True)
+    ref = ow.trace(o, d, norm_mode=ol.NORM_HOST)
+    assert_same_hits(full, ref, counters=True)
+    sub = rt.raytrace(o, d, norm_mode=vx.NORM_HOST, planes=rt.REFERENCE_PLANES)
+    assert sorted(sub) == sorted(rt.REFERENCE_PLANES)
+    for k in rt.REFERENCE_PLANES:
+        assert np.array_equal(sub[k].view(np.uint8), full[k].view(np.uint8)), k
+    one = rt.raytrace(o, d, norm_mode=vx.NORM_HOST, planes=("brick",), out=dict(brick=np.full(n, 7, np.uint32)))
+    assert np.array_equal(one["brick"], full["brick"])
+    # a second call reuses ring, threads and streams; a small batch takes the plain path
+    again = rt.raytrace(o[:1000], d[:1000], norm_mode=vx.NORM_HOST)
+    for k in INT_PLANES:
+        assert np.array_equal(again[k], full[k][:1000])
+    rt.close()

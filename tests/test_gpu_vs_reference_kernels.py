@@ -115,3 +115,47 @@ def test_ortho_frame_equals_reference_ortho_build(vx, my_world, tmp_path, view):
     persp = rt.render_host(vx.make_camera(pos, eul, 90.0), vx.default_env(), opts, W, H, bgra=np.full((H, W, 4), 255, np.uint8))
     assert not np.array_equal(persp, ref)
     rt.close()
+
+
+REF_SHADED = os.path.join(ol.ORACLE_DIR, "_ref", "ref_gpu_nofma_shaded")
+
+
+@pytest.mark.skipif(not os.path.exists(REF_SHADED), reason="oracle/_ref/ref_gpu_nofma_shaded not built")
+@pytest.mark.parametrize("view", [((512, None, 960), (-0.45, 0.0, 0.0)), ((300, None, 300), (-0.1, 0.8, 0.0))])
+def test_shaded_shadowed_frame_equals_reference_shaded_build(vx, tmp_path, view):
+    """BASELINE config 2 at its stated size: 1024x256x1024 world, 1920x1080, primary + sun-shadow rays, shaded.  The
+    reference ships this branch compiled out (Renderer.cu:4 `#define DEBUG_VIEW`) with the shadow Raytrace commented out
+    (:102); oracle/Makefile restores both on a scratch copy (ref_gpu_nofma_shaded), everything else is the reference's own
+    source.  calculateColor + Tonemap + setPixelColor (:72-177) on the reference's kernel vs ours: the checkerboard half of
+    frame 0 and the filled buffer after frame 1, within 1/255 per channel (powf and rsqrtf are the same device functions
+    on both sides, so byte-identical is what we expect and report)."""
+    DIMS1 = (1024, 256, 1024)
+    (px, _, pz), eul = view
+    W, H = 1920, 1080
+    w = vx.World.from_noise(*DIMS1, FACTOR)
+    probe = vx.VoxelRaytracer3D(w, 4)
+    r = probe.raytrace(np.array([[px + 0.5, DIMS1[1] + 10.0, pz + 0.5]], np.float32), np.array([[0, -1, 0]], np.float32))
+    probe.close()
+    top_y = int(r["voxel"][0, 1]) if r["hit"][0] else -1
+    pos = (px, (top_y + 16 if top_y < DIMS1[1] - 1 else DIMS1[1] + 32), pz)  # camera height rule of SURVEY.md 8d
+    out, last = tmp_path / "frame0.bgra", tmp_path / "frame1.bgra"
+    res = subprocess.run([REF_SHADED] + [str(a) for a in ["render", *DIMS1, FACTOR, W, H, *pos, *eul, 2, out]],
+                         capture_output=True, text=True, timeout=900, env=dict(os.environ, VXREF_DUMP_LAST=str(last)))
+    assert res.returncode == 0, res.stderr[-2000:]
+    ref0 = np.fromfile(out, np.uint8).reshape(H, W, 4)
+    ref1 = np.fromfile(last, np.uint8).reshape(H, W, 4)
+    rt = vx.VoxelRaytracer3D(w, 1)
+    cam = vx.make_camera(pos, eul, 90.0)
+    buf = np.full((H, W, 4), 255, np.uint8)
+    got0 = rt.render_host(cam, vx.default_env(), vx.RenderOpts(1, 0, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None), W, H, bgra=buf).copy()
+    got1 = rt.render_host(cam, vx.default_env(), vx.RenderOpts(1, 1, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None), W, H, bgra=buf).copy()
+    rt.close(); w.close()
+    for name, got, ref in (("frame 0", got0, ref0), ("frames 0+1", got1, ref1)):
+        assert (ref[..., :3] != 255).any(), "reference frame is empty"
+        diff = np.abs(got.astype(np.int16) - ref.astype(np.int16))
+        nd = int((diff > 0).any(2).sum())
+        print("%s: %d of %d pixels differ, max channel difference %d" % (name, nd, W * H, int(diff.max())))
+        assert diff.max() <= 1, "%s: max channel difference %d at %d pixels" % (name, diff.max(), nd)
+        assert nd <= W * H // 1000
+    # shadows make a difference in this scene (the pin would be empty otherwise), and frame 1 fills what frame 0 left
+    assert (ref1[1:-2] != 255).any(2).mean() > 0.99

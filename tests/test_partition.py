@@ -85,3 +85,18 @@ def test_band_ownership_covers_every_row_once():
 def test_rank_outside_world_is_rejected():
     with pytest.raises(ValueError):
         FramePartition(8, 8, 2, 2)
+
+
+def test_checkerboard_partitions_refuse_row_copies():
+    """A checkerboard frame's bands interleave in pixel space (thread row ty writes pixel rows 2 ty .. 2 ty + 2), so the
+    paths that move whole pixel rows must refuse it instead of assembling stale rows."""
+    part = FramePartition(64, 64, 2, 0, checkerboard=True)
+    with pytest.raises(ValueError):
+        part.gather(part.alloc_frame("cpu"))
+    with pytest.raises(ValueError):
+        part.render_and_gather(part.alloc_frame("cpu"), lambda y0, h: None, 2)
+    from voxelengine_b200.partition import HostFrame
+    with pytest.raises(ValueError):
+        HostFrame(part, 0)
+    single = FramePartition(64, 64, 1, 0, checkerboard=True)   # one rank: nothing to move, nothing to refuse
+    assert single.gather(single.alloc_frame("cpu")) is not None

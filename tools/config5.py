@@ -20,7 +20,7 @@ w1_ms = small.info.build_ms
 small.close()
 W, H = wl["W"], wl["H"]
 rt = vx.VoxelRaytracer3D(world, 16)
-cam, pos = bench.camera_for(vx, rt, wl)
+cam, pos = bench.camera_for(vx, rt, wl["dims"], bench.CAMERAS[os.environ["VX_CAMERA"]] if os.environ.get("VX_CAMERA") else bench.camera_spec(wl))
 opts = vx.RenderOpts(0, 0, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None)
 d_o = torch.zeros(W * H * 3, dtype=torch.float32, device="cuda")
 d_d = torch.zeros(W * H * 3, dtype=torch.float32, device="cuda")

@@ -9,7 +9,7 @@ name = sys.argv[1] if len(sys.argv) > 1 else "w2-4k"
 wl = bench.WORKLOADS[name]
 world = vx.World.from_noise(*wl["dims"], 8)
 rt = vx.VoxelRaytracer3D(world, 16)
-cam, pos = bench.camera_for(vx, rt, wl)
+cam, pos = bench.camera_for(vx, rt, wl["dims"], bench.CAMERAS[os.environ["VX_CAMERA"]] if os.environ.get("VX_CAMERA") else bench.camera_spec(wl))
 W, H = wl["W"], wl["H"]
 buf = torch.zeros(H * W * 4, dtype=torch.uint8, device="cuda")
 for shadows in (0, 1):

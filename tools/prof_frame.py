@@ -10,7 +10,7 @@ frames = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 wl = bench.WORKLOADS[name]
 world = vx.World.from_noise(*wl["dims"], 8)
 rt = vx.VoxelRaytracer3D(world, 16)
-cam, pos = bench.camera_for(vx, rt, wl)
+cam, pos = bench.camera_for(vx, rt, wl["dims"], bench.CAMERAS[os.environ["VX_CAMERA"]] if os.environ.get("VX_CAMERA") else bench.camera_spec(wl))
 W, H = wl["W"], wl["H"]
 buf = torch.zeros(H * W * 4, dtype=torch.uint8, device="cuda")
 opts = vx.RenderOpts(0, 0, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None)

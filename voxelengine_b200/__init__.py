@@ -31,7 +31,7 @@ class WorldInfo(C.Structure):
     _fields_ = [("dims", C.c_uint32 * 3), ("coarse", C.c_uint32 * 3), ("factor", C.c_int32), ("device", C.c_int32),
                 ("bricks", C.c_uint64), ("occupied_bricks", C.c_uint64), ("solid_voxels", C.c_uint64),
                 ("bytes_top", C.c_uint64), ("bytes_records", C.c_uint64), ("bytes_pool", C.c_uint64),
-                ("build_ms", C.c_float)]
+                ("build_ms", C.c_float), ("tiles_ms", C.c_float)]
 
 
 class Hits(C.Structure):
@@ -64,10 +64,10 @@ class RenderOpts(C.Structure):
 # Every symbol include/vxrt.h declares (tests check that the library exports all of them).
 ABI_SYMBOLS = [
     "vx_last_error", "vx_version", "vx_device_count", "vx_world_build_noise", "vx_world_build_noise_full",
-    "vx_world_from_dense_bits", "vx_world_destroy", "vx_world_get_info", "vx_world_download", "vx_tracer_create",
+    "vx_world_from_dense_bits", "vx_world_destroy", "vx_world_get_info", "vx_world_download", "vx_world_download_bricks", "vx_tracer_create",
     "vx_tracer_destroy", "vx_trace", "vx_trace_device", "vx_hits_postprocess", "vx_get_directions", "vx_render",
     "vx_render_host", "vx_bounce_rays", "vx_tracer_set_timing", "vx_tracer_set_fused_shade", "vx_tracer_frame_times", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
-    "vx_shared_alloc", "vx_shared_open", "vx_shared_close", "vx_shared_free", "vx_device_to_host",
+    "vx_shared_alloc", "vx_shared_open", "vx_shared_close", "vx_shared_free", "vx_device_to_host", "vx_device_fill",
     "vx_host_register", "vx_host_unregister", "vx_bands_to_host",
     "vx_world_edit", "vx_world_save", "vx_world_load",
 ]
@@ -93,6 +93,7 @@ def lib():
     L.vx_world_destroy.argtypes = [vp]
     L.vx_world_get_info.argtypes = [vp, C.POINTER(WorldInfo)]
     L.vx_world_download.argtypes = [vp, vp, vp, vp]
+    L.vx_world_download_bricks.argtypes = [vp, vp, sz, vp, vp, vp]
     L.vx_tracer_create.argtypes = [C.POINTER(vp), vp, sz]
     L.vx_tracer_destroy.argtypes = [vp]
     L.vx_trace.argtypes = [vp, vp, vp, sz, C.POINTER(TraceOpts), C.POINTER(Hits)]
@@ -114,6 +115,7 @@ def lib():
     L.vx_shared_close.argtypes = [vp, i32]
     L.vx_shared_free.argtypes = [vp, i32]
     L.vx_device_to_host.argtypes = [vp, vp, sz, i32, vp]
+    L.vx_device_fill.argtypes = [vp, i32, sz, i32, vp]
     L.vx_world_edit.argtypes = [vp, vp, sz, i32]
     L.vx_world_save.argtypes = [vp, C.c_char_p]
     L.vx_world_load.argtypes = [C.POINTER(vp), C.c_char_p, i32]
@@ -210,6 +212,10 @@ def device_to_host(host_ptr, dev_ptr, nbytes, device=0, stream=0):
     _check(lib().vx_device_to_host(host_ptr, dev_ptr, int(nbytes), device, stream))
 
 
+def device_fill(dev_ptr, byte, nbytes, device=0, stream=0):
+    _check(lib().vx_device_fill(dev_ptr, int(byte), int(nbytes), device, stream))
+
+
 def host_register(ptr, nbytes):
     _check(lib().vx_host_register(ptr, int(nbytes)))
 
@@ -296,6 +302,24 @@ class World:
         _check(lib().vx_world_download(self.h, top.ctypes.data, bw.ctypes.data, b6.ctypes.data))
         return top, bw, b6
 
+    def download_top(self):
+        """The top-level occupancy bits alone (reference tiled index)."""
+        top = np.zeros((int(self.info.bricks) + 31) // 32, np.uint32)
+        _check(lib().vx_world_download(self.h, top.ctypes.data, None, None))
+        return top
+
+    def download_bricks(self, coarse_xyz):
+        """(occupied[n], brick_words[n, factor^3/32], bounds[n, 6]) of the bricks at the given coarse coordinates, in the
+        reference's form; occupied bit 0 = traversal grid's top-level bit, bit 1 = the reference-indexed one."""
+        c = np.ascontiguousarray(coarse_xyz, np.uint32).reshape(-1, 3)
+        n = c.shape[0]
+        wpb = self.info.factor ** 3 // 32
+        occ = np.zeros(n, np.uint8)
+        bw = np.zeros((n, wpb), np.uint32)
+        b6 = np.zeros((n, 6), np.float32)
+        _check(lib().vx_world_download_bricks(self.h, c.ctypes.data, n, occ.ctypes.data, bw.ctypes.data, b6.ctypes.data))
+        return occ, bw, b6
+
 
 class VoxelRaytracer3D:
     """GPUDDA::VoxelRaytracer3D (VolumeRaytracer.cuh:291-377): ray buffers for `count` rays bound to a world."""
@@ -317,28 +341,38 @@ class VoxelRaytracer3D:
         except Exception:
             pass
 
-    def raytrace(self, origins, dirs, norm_mode=NORM_DEVICE, max_steps=0, counters=False):
+    PLANES = dict(hit=(np.uint8, 1), pos=(np.float32, 3), normal=(np.float32, 3), steps=(np.int32, 1), voxel=(np.int32, 3),
+                  brick=(np.uint32, 1), coarse_steps=(np.int32, 1), fine_steps=(np.int32, 1), counters=(np.uint32, 3))
+    REFERENCE_PLANES = ("hit", "pos", "normal", "steps")  # what the reference's own Raytrace returns (VolumeRaytracer.cu:590-599)
+
+    def raytrace(self, origins, dirs, norm_mode=NORM_DEVICE, max_steps=0, counters=False, planes=None, out=None):
         """VoxelRaytracer3D::Raytrace (VolumeRaytracer.cu:574-618) with host arrays.
         Returns a dict of numpy planes (hit, pos, normal, steps, voxel, brick, coarse_steps, fine_steps
-        [, counters]) plus the reference's host-derived valid / distance."""
+        [, counters]) plus the reference's host-derived valid / distance.  `planes` restricts the result to the named
+        planes (only those are computed, copied down and returned; valid / distance need "pos"); `out` reuses the arrays
+        of an earlier call instead of allocating."""
         o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
         d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
         n = o.shape[0]
         if d.shape[0] != n:
             raise VxError("origins and dirs differ in length")
-        out = dict(hit=np.zeros(n, np.uint8), pos=np.zeros((n, 3), np.float32), normal=np.zeros((n, 3), np.float32),
-                   steps=np.zeros(n, np.int32), voxel=np.zeros((n, 3), np.int32), brick=np.zeros(n, np.uint32),
-                   coarse_steps=np.zeros(n, np.int32), fine_steps=np.zeros(n, np.int32))
-        if counters:
-            out["counters"] = np.zeros((n, 3), np.uint32)
-        h = Hits(**{k: v.ctypes.data for k, v in out.items()})
+        names = [k for k in self.PLANES if k != "counters"] + (["counters"] if counters else []) if planes is None else list(planes)
+        res = {}
+        for k in names:
+            dt, w = self.PLANES[k]
+            a = out.get(k) if out else None
+            if a is None or a.dtype != dt or a.shape != ((n, w) if w > 1 else (n,)):
+                a = np.zeros((n, w) if w > 1 else n, dt)
+            res[k] = a
+        h = Hits(**{k: v.ctypes.data for k, v in res.items()})
         opts = TraceOpts(norm_mode, max_steps)
         _check(lib().vx_trace(self.h, o.ctypes.data, d.ctypes.data, n, C.byref(opts), C.byref(h)))
-        out["valid"] = np.zeros(n, np.uint8)
-        out["distance"] = np.zeros(n, np.float32)
-        _check(lib().vx_hits_postprocess(o.ctypes.data, out["pos"].ctypes.data, n, out["valid"].ctypes.data,
-                                         out["distance"].ctypes.data))
-        return out
+        if "pos" in res and planes is None:
+            res["valid"] = np.zeros(n, np.uint8)
+            res["distance"] = np.zeros(n, np.float32)
+            _check(lib().vx_hits_postprocess(o.ctypes.data, res["pos"].ctypes.data, n, res["valid"].ctypes.data,
+                                             res["distance"].ctypes.data))
+        return res
 
     def raytrace_device(self, d_origins, d_dirs, n, planes, norm_mode=NORM_DEVICE, max_steps=0, stream=0):
         """Device-pointer variant: `planes` maps plane name -> device pointer (int)."""

@@ -4,6 +4,7 @@
 // world is, bit for bit, what a rebuild from the edited dense grid would give (top-level bits, brick masks, bounds), so
 // every parity statement about traversal carries over.
 #include "vx_host.h"
+#include <stddef.h>
 
 #include <cstring>
 #include <vector>
@@ -180,7 +181,7 @@ struct FileHeader {
     uint32_t version, X, Y, Z, factor, words_per_brick, reserved;
     uint64_t nbricks, occupied, solid_voxels, pool_used;
     uint64_t bytes_top, bytes_ptop, bytes_precords, bytes_pool;
-    uint64_t checksum; // FNV-1a over the four payload sections
+    uint64_t checksum; // FNV-1a over the header up to this field, then the four payload sections
 };
 const char kMagic[8] = {'V', 'X', 'B', 'R', 'I', 'C', 'K', '1'};
 
@@ -194,6 +195,21 @@ void section_sizes(const vx_world* w, uint64_t out[4]) {
     out[0] = (w->nbricks + 31) / 32 * 4; out[1] = (pcells + 31) / 32 * 4; out[2] = pcells * 8; out[3] = w->pool_used * w->words_per_brick * 4;
 }
 constexpr size_t kChunk = 64u << 20;
+constexpr uint32_t kFileVersion = 2; // 2: the checksum covers the header too
+
+// What the march relies on without checking: every border cell of the traversal grid reads as occupied, and every
+// occupied interior cell's record points into the pool.  Counts violations.
+__global__ void validate_traversal_grid(const uint32_t* __restrict__ ptop, const uint2* __restrict__ precords, uint32_t cx, uint32_t cy, uint32_t cz,
+                                        uint64_t pcells, uint64_t pool_used, unsigned long long* __restrict__ bad) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pcells) return;
+    const uint32_t pnx = cx + 2u, pny = cy + 2u;
+    const uint32_t x = (uint32_t)(p % pnx), y = (uint32_t)((p / pnx) % pny), z = (uint32_t)(p / ((uint64_t)pnx * pny));
+    const bool border = x == 0u || y == 0u || z == 0u || x == cx + 1u || y == cy + 1u || z == cz + 1u;
+    const bool bit = (ptop[p >> 5] >> (p & 31u)) & 1u;
+    const bool wrong = border ? !bit : (bit && (uint64_t)precords[p].y >= pool_used);
+    if (wrong) atomicAdd(bad, 1ull);
+}
 } // namespace
 
 extern "C" int vx_world_save(const vx_world* w, const char* path) {
@@ -204,7 +220,7 @@ extern "C" int vx_world_save(const vx_world* w, const char* path) {
     VX_REQUIRE(f != nullptr, std::string("cannot open for writing: ") + path);
     FileHeader h{};
     memcpy(h.magic, kMagic, 8);
-    h.version = 1; h.X = w->X; h.Y = w->Y; h.Z = w->Z; h.factor = (uint32_t)w->factor; h.words_per_brick = w->words_per_brick;
+    h.version = kFileVersion; h.X = w->X; h.Y = w->Y; h.Z = w->Z; h.factor = (uint32_t)w->factor; h.words_per_brick = w->words_per_brick;
     h.nbricks = w->nbricks; h.occupied = w->occupied; h.solid_voxels = w->solid_voxels; h.pool_used = w->pool_used;
     uint64_t sz[4];
     section_sizes(w, sz);
@@ -212,7 +228,7 @@ extern "C" int vx_world_save(const vx_world* w, const char* path) {
     const void* src[4] = {w->d_top, w->d_ptop, w->d_precords, w->d_pool};
     std::vector<uint8_t> buf(kChunk);
     bool ok = fwrite(&h, sizeof h, 1, f) == 1;
-    uint64_t sum = 14695981039346656037ull;
+    uint64_t sum = fnv1a(14695981039346656037ull, &h, offsetof(FileHeader, checksum));
     for (int s = 0; s < 4 && ok; ++s)
         for (uint64_t off = 0; off < sz[s] && ok; off += kChunk) {
             const size_t m = (size_t)(sz[s] - off < kChunk ? sz[s] - off : kChunk);
@@ -234,7 +250,7 @@ extern "C" int vx_world_load(vx_world** out, const char* path, int device) {
     FILE* f = fopen(path, "rb");
     VX_REQUIRE(f != nullptr, std::string("cannot open: ") + path);
     FileHeader h{};
-    if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, kMagic, 8) != 0 || h.version != 1) { fclose(f); VX_REQUIRE(false, "not a VXBRICK1 file"); }
+    if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, kMagic, 8) != 0 || h.version != kFileVersion) { fclose(f); VX_REQUIRE(false, "not a VXBRICK1 file of this version"); }
     DeviceGuard guard(device);
     vx_world* w = new vx_world();
     w->device = device; w->X = h.X; w->Y = h.Y; w->Z = h.Z; w->factor = (int)h.factor; w->words_per_brick = h.words_per_brick;
@@ -245,14 +261,17 @@ extern "C" int vx_world_load(vx_world** out, const char* path, int device) {
         w->pool_used = h.pool_used; w->pool_capacity = h.pool_used ? h.pool_used : 1;
         uint64_t sz[4];
         section_sizes(w, sz);
-        sane = w->cx % 8 == 0 && w->cy % 8 == 0 && w->cz % 8 == 0 && h.nbricks == w->nbricks && h.words_per_brick == h.factor * h.factor * h.factor / 32 &&
+        // the invariants the builders enforce (check_dims, finish_build): uint16 coarse dims, 32-bit brick index, 31-bit padded cell index
+        const uint64_t pcells = (uint64_t)(w->cx + 2) * (w->cy + 2) * (w->cz + 2);
+        sane = w->cx <= 65535u && w->cy <= 65535u && w->cz <= 65535u && w->nbricks < (1ull << 32) && pcells < (1ull << 31) &&
+               w->cx % 8 == 0 && w->cy % 8 == 0 && w->cz % 8 == 0 && h.nbricks == w->nbricks && h.words_per_brick == h.factor * h.factor * h.factor / 32 &&
                h.pool_used <= w->nbricks && h.occupied <= h.pool_used && sz[0] == h.bytes_top && sz[1] == h.bytes_ptop && sz[2] == h.bytes_precords && sz[3] == h.bytes_pool;
     }
     if (!sane) { fclose(f); delete w; VX_REQUIRE(false, "inconsistent header"); }
     const uint64_t sz[4] = {h.bytes_top, h.bytes_ptop, h.bytes_precords, h.bytes_pool};
     void** dst[4] = {(void**)&w->d_top, (void**)&w->d_ptop, (void**)&w->d_precords, (void**)&w->d_pool};
     std::vector<uint8_t> buf(kChunk);
-    uint64_t sum = 14695981039346656037ull;
+    uint64_t sum = fnv1a(14695981039346656037ull, &h, offsetof(FileHeader, checksum));
     const char* why = nullptr;
     for (int s = 0; s < 4 && !why; ++s) {
         const size_t alloc = (size_t)(s == 3 ? w->pool_capacity * w->words_per_brick * 4 : sz[s]);
@@ -266,6 +285,18 @@ extern "C" int vx_world_load(vx_world** out, const char* path, int device) {
     }
     fclose(f);
     if (!why && sum != h.checksum) why = "checksum mismatch";
+    if (!why) { // a file that passes the checksum may still come from elsewhere: check what the march takes on trust
+        unsigned long long* d_bad = nullptr;
+        unsigned long long bad = 0;
+        const uint64_t pcells = (uint64_t)(w->cx + 2) * (w->cy + 2) * (w->cz + 2);
+        if (cudaMalloc(&d_bad, 8) != cudaSuccess || cudaMemset(d_bad, 0, 8) != cudaSuccess) why = "out of device memory";
+        else {
+            validate_traversal_grid<<<(unsigned)((pcells + 255) / 256), 256>>>(w->d_ptop, w->d_precords, w->cx, w->cy, w->cz, pcells, w->pool_used, d_bad);
+            if (cudaMemcpy(&bad, d_bad, 8, cudaMemcpyDeviceToHost) != cudaSuccess) why = "validation failed to run";
+            else if (bad) why = "traversal grid is inconsistent (border bits or pool slots)";
+        }
+        cudaFree(d_bad);
+    }
     if (why) {
         cudaGetLastError();
         cudaFree(w->d_top); cudaFree(w->d_ptop); cudaFree(w->d_precords); cudaFree(w->d_pool);

@@ -61,7 +61,7 @@ struct vx_world {
     uint2* d_precords = nullptr; // padded linear records (traversal)
     uint32_t* d_pool = nullptr;  // pool_capacity * words_per_brick; slots >= pool_used are zero
     uint64_t pool_capacity = 0, pool_used = 0; // in bricks; vx_world_edit hands out slots pool_used.. and grows the pool
-    float build_ms = 0.0f;
+    float build_ms = 0.0f, tiles_ms = 0.0f;
     vx::WorldView view() const {
         vx::WorldView v;
         v.top = d_top; v.records = d_records; v.pool = d_pool;
@@ -74,6 +74,7 @@ struct vx_world {
     }
 };
 
+namespace vx { struct BatchPipe; void destroy_batch_pipe(BatchPipe*); }
 constexpr unsigned kNextSlots = 64;
 struct vx_tracer {
     vx_world* world = nullptr;
@@ -103,5 +104,6 @@ struct vx_tracer {
     int fused_shade = 0;  // vx_tracer_set_fused_shade
     bool primary_only = false; unsigned long long* last_queue_count = nullptr; // vx_bounce_rays reuses vx_render's primary pass
     cudaStream_t l2_stream = nullptr; const void* l2_base = nullptr; bool l2_tried = false; // pin_top_level (vx_trace.cu)
+    vx::BatchPipe* batch = nullptr; // vx_trace: pinned staging ring, copy threads and streams of the host-array batch call
     bool timing = false; int timed_kernels = 0; cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // vx_tracer_set_timing
 };

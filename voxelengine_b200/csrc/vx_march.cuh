@@ -21,10 +21,11 @@ enum : uint32_t { ST_IDLE = 0, ST_BEGIN = 1, ST_FAST = 2, ST_SLOW = 3, ST_CAND =
 constexpr uint32_t F_ST = 7u;          // bits 0-2: state
 constexpr uint32_t F_SLOW = 1u << 3;   // traversal runs in the generic (bounds-checked, reference-ordered) mode
 constexpr uint32_t F_EDGE = 1u << 4;   // IsOnEdge at the start of this traversal (VolumeRaytracer.cu:216-232)
-constexpr uint32_t F_CAPOK = 1u << 5;  // the border is reached within kMaxSteps examinations and no tMax is NaN
+constexpr uint32_t F_CAPOK = 1u << 5;  // no tMax is NaN: the fast loop's step is the reference's comparison chain
 constexpr uint32_t F_HIT = 1u << 6;
 constexpr uint32_t F_SHADOW = 1u << 7; // render: this lane marches the shadow ray of its pixel
 constexpr int F_SN_SHIFT = 8;          // bits 8-10: normal code of the grid-entry clip (start_normal)
+constexpr uint32_t F_NEAR = 1u << 11;  // the kMaxSteps cap can be reached before the border: the fast loop checks per chunk
 
 // Axis-aligned unit normals as a 3-bit code: 0 = (0,0,0); 1 + 2*axis + (negative ? 1 : 0).
 __device__ __forceinline__ V3 normal_from_code(uint32_t c) {
@@ -113,7 +114,7 @@ __device__ __forceinline__ void lane_setup(const WorldView& w, Lane& L, V3 s, V3
 // Start of one coarse DDARayTraversal (VolumeRaytracer.cu:186-232) from L.s; also the `while (total_steps <
 // maxSteps)` test of Raytrace (:383).
 __device__ __forceinline__ void lane_begin(const WorldView& w, Lane& L, int max_steps) {
-    L.flags &= ~(F_SLOW | F_EDGE | F_CAPOK);
+    L.flags &= ~(F_SLOW | F_EDGE | F_CAPOK | F_NEAR);
     if (!(L.total < max_steps)) { lane_set_state(L, ST_DONE); return; }
     const int x0 = (int)L.s.x, y0 = (int)L.s.y, z0 = (int)L.s.z; // cvt.rzi: truncation, saturating, NaN -> 0
     const int ox = L.d.x > 0.0f, oy = L.d.y > 0.0f, oz = L.d.z > 0.0f;
@@ -126,12 +127,13 @@ __device__ __forceinline__ void lane_begin(const WorldView& w, Lane& L, int max_
     L.idx = index_of(w, x0, y0, z0);
     const bool on_edge = x0 == w.cx || y0 == w.cy || z0 == w.cz;
     const bool no_nan = L.tx == L.tx && L.ty == L.ty && L.tz == L.tz;
-    // examinations needed to reach the border along every axis: the fast loop carries no step counter, so the
-    // kMaxSteps cap (:236) must be unreachable before a border cell (which ends the traversal) is examined
+    // examinations needed to reach the border along every axis: the fast loop carries no step counter, so where the
+    // kMaxSteps cap (:236) could come before a border cell (which ends the traversal) the loop re-derives the count
+    // from the cell index before every chunk of kFastChunk steps (F_NEAR) and hands the last stretch to lane_slow
     const int reach = (ox ? w.cx - x0 : x0 + 1) + (oy ? w.cy - y0 : y0 + 1) + (oz ? w.cz - z0 : z0 + 1);
-    const bool capok = no_nan && reach < kMaxSteps;
+    const bool capok = no_nan;
     const bool fast = capok && interior(w, x0, y0, z0);
-    L.flags |= (on_edge ? F_EDGE : 0u) | (capok ? F_CAPOK : 0u) | (fast ? 0u : F_SLOW);
+    L.flags |= (on_edge ? F_EDGE : 0u) | (capok ? F_CAPOK : 0u) | (fast ? 0u : F_SLOW) | (reach < kMaxSteps ? 0u : F_NEAR);
     lane_set_state(L, fast ? ST_FAST : ST_SLOW);
 }
 
@@ -149,14 +151,50 @@ __device__ __forceinline__ void lane_step(const WorldView& w, Lane& L) {
     L.idx += (uint32_t)(mx ? dix : (my ? diy : diz));
 }
 
+#ifndef VX_REFILL_MIN
+#define VX_REFILL_MIN 8
+#endif
+#ifndef VX_FAST_CHUNK
+#define VX_FAST_CHUNK 64
+#endif
+// Fast-loop scheduling, per ray source (Policy::kFastQuad, kLeaveNum / kLeaveDen): steps between looks at how many lanes are
+// still stepping, and the share of the lanes that entered below which the rest stop too.  Measured per 4K frame (profiles/):
+// primaries 4 steps, 1/4: 1.41 ms; 8 steps: 1.37 (1/4 and 1/2 alike); sun rays 4 steps, 1/4: 1.00 ms; 4 steps, 1/2: 0.95-0.96;
+// incoherent bounce rays (batch kernel) 4 steps, 1/4: 2.30 ms; 8 steps: 2.25; 1/2: 2.46.
+#ifndef VX_PRIMARY_QUAD
+#define VX_PRIMARY_QUAD 8
+#endif
+#ifndef VX_PRIMARY_LEAVE_NUM
+#define VX_PRIMARY_LEAVE_NUM 1
+#define VX_PRIMARY_LEAVE_DEN 2
+#endif
+#ifndef VX_SHADOW_QUAD
+#define VX_SHADOW_QUAD 4
+#endif
+#ifndef VX_SHADOW_LEAVE_NUM
+#define VX_SHADOW_LEAVE_NUM 1
+#define VX_SHADOW_LEAVE_DEN 2
+#endif
+#ifndef VX_BATCH_QUAD
+#define VX_BATCH_QUAD 8
+#endif
+#ifndef VX_BATCH_LEAVE_NUM
+#define VX_BATCH_LEAVE_NUM 1
+#define VX_BATCH_LEAVE_DEN 4
+#endif
+constexpr int kChunk = 32;                  // ray ids a warp draws at a time (render: one 8x4 pixel tile)
+constexpr int kFastChunk = VX_FAST_CHUNK;   // coarse steps a lane may take before the warp looks at the other states again
+
 // Generic mode: one bounds-checked examination + step per call (the ray starts outside the grid, sits on the padded
 // far face, carries NaNs, or could reach the step cap).  Rare; exactness over speed.
 template <bool COUNT>
 __device__ __forceinline__ void lane_slow(const WorldView& w, Lane& L) {
     int x, y, z;
     cell_of(w, L.idx, x, y, z);
-    if ((L.flags & F_CAPOK) && interior(w, x, y, z)) { L.flags &= ~F_SLOW; lane_set_state(L, ST_FAST); return; }
     const int it = steps_from_start(L, x, y, z);
+    if ((L.flags & F_CAPOK) && interior(w, x, y, z) && (!(L.flags & F_NEAR) || it + kFastChunk <= kMaxSteps)) {
+        L.flags &= ~F_SLOW; lane_set_state(L, ST_FAST); return;
+    }
     const bool edge = L.flags & F_EDGE;
     const int limx = w.cx + ((edge && L.d.x < 0.0f) ? 1 : 0), limy = w.cy + ((edge && L.d.y < 0.0f) ? 1 : 0),
               limz = w.cz + ((edge && L.d.z < 0.0f) ? 1 : 0);
@@ -438,47 +476,19 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 //   kRefill                               idle lanes that trigger a refill (32: whole tiles only)
 //   kFastQuad, kLeaveNum, kLeaveDen       fast-loop scheduling, see lane_fast
 //   kDrain, void drain(uint32_t done)     kDrain: called by all 32 lanes once per round, after finish(), with the ballot of the
-//                                         lanes that finished this round (a policy batching its per-ray epilogue across the warp)
+//                                         lanes that finished this round (a policy batching its per-ray epilogue across the warp);
+//                                         the same ballot is in pol.done_ballot while finish() runs
 // `next` is a zero-initialised device counter shared by all warps of the launch.
 // ---------------------------------------------------------------------------------------------
-#ifndef VX_REFILL_MIN
-#define VX_REFILL_MIN 8
-#endif
-#ifndef VX_FAST_CHUNK
-#define VX_FAST_CHUNK 64
-#endif
-// Fast-loop scheduling, per ray source (Policy::kFastQuad, kLeaveNum / kLeaveDen): steps between looks at how many lanes are
-// still stepping, and the share of the lanes that entered below which the rest stop too.  Measured per 4K frame (profiles/):
-// primaries 4 steps, 1/4: 1.41 ms; 8 steps: 1.37 (1/4 and 1/2 alike); sun rays 4 steps, 1/4: 1.00 ms; 4 steps, 1/2: 0.95-0.96;
-// incoherent bounce rays (batch kernel) 4 steps, 1/4: 2.30 ms; 8 steps: 2.25; 1/2: 2.46.
-#ifndef VX_PRIMARY_QUAD
-#define VX_PRIMARY_QUAD 8
-#endif
-#ifndef VX_PRIMARY_LEAVE_NUM
-#define VX_PRIMARY_LEAVE_NUM 1
-#define VX_PRIMARY_LEAVE_DEN 2
-#endif
-#ifndef VX_SHADOW_QUAD
-#define VX_SHADOW_QUAD 4
-#endif
-#ifndef VX_SHADOW_LEAVE_NUM
-#define VX_SHADOW_LEAVE_NUM 1
-#define VX_SHADOW_LEAVE_DEN 2
-#endif
-#ifndef VX_BATCH_QUAD
-#define VX_BATCH_QUAD 8
-#endif
-#ifndef VX_BATCH_LEAVE_NUM
-#define VX_BATCH_LEAVE_NUM 1
-#define VX_BATCH_LEAVE_DEN 4
-#endif
-constexpr int kChunk = 32;                  // ray ids a warp draws at a time (render: one 8x4 pixel tile)
-constexpr int kFastChunk = VX_FAST_CHUNK;   // coarse steps a lane may take before the warp looks at the other states again
-
 // ST_FAST: the hot loop over the bordered linear grid; leaving the grid shows up as an occupied (border) cell.
 template <bool COUNT, int QUAD, int LEAVE_NUM, int LEAVE_DEN>
 __device__ __forceinline__ void lane_fast(const WorldView& w, Lane& L) {
     static_assert(kFastChunk % QUAD == 0, "the step budget is counted in quads");
+    if (L.flags & F_NEAR) { // rare (corner-to-corner views of the largest worlds): is a whole chunk still below the step cap?
+        int x, y, z;
+        cell_of(w, L.idx, x, y, z);
+        if (steps_from_start(L, x, y, z) + kFastChunk > kMaxSteps) { L.flags |= F_SLOW; lane_set_state(L, ST_SLOW); return; }
+    }
     const float dtx = lane_dt(L.d.x, L.ivx), dty = lane_dt(L.d.y, L.ivy), dtz = lane_dt(L.d.z, L.ivz);
     const int dix = L.d.x > 0.0f ? 1 : -1, diy = L.d.y > 0.0f ? w.pnx : -w.pnx, diz = L.d.z > 0.0f ? w.pnxy : -w.pnxy;
     float tx = L.tx, ty = L.ty, tz = L.tz;
@@ -525,6 +535,7 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
         if (lane_state(L) == ST_CAND) lane_cand<BATCH, COUNT>(w, L, pos, ncode);
         if constexpr (Policy::kDrain) {
             const uint32_t done = __ballot_sync(kFull, lane_state(L) == ST_DONE);
+            pol.done_ballot = done; // finish() places its result by rank within this ballot, not by whoever happens to be converged
             if (lane_state(L) == ST_DONE) pol.finish(w, L, pos, ncode);
             if (done) pol.drain(done);
         } else {

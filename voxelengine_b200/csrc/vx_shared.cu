@@ -49,6 +49,14 @@ extern "C" int vx_shared_free(void* d_ptr, int device) {
     return VX_OK;
 }
 
+extern "C" int vx_device_fill(void* d_dst, int byte, size_t bytes, int device, void* stream) {
+    VX_REQUIRE(d_dst != nullptr, "NULL argument");
+    DeviceGuard guard(device);
+    VX_CUDA(cudaMemsetAsync(d_dst, byte, bytes, (cudaStream_t)stream));
+    VX_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return VX_OK;
+}
+
 extern "C" int vx_device_to_host(void* h_dst, const void* d_src, size_t bytes, int device, void* stream) {
     VX_REQUIRE(h_dst && d_src, "NULL argument");
     DeviceGuard guard(device);

@@ -7,6 +7,11 @@
 #include "vx_host.h"
 #include "vx_march.cuh"
 #include <stdlib.h>
+#include <string.h>
+#include <condition_variable>
+#include <mutex>
+#include <thread>
+#include <vector>
 
 #ifndef VX_TILE_SHAPE
 #define VX_TILE_SHAPE 0 // pixels a warp of primary_rays takes at a time: 0 = 8x4, 1 = 16x2, 2 = 32x1
@@ -388,9 +393,10 @@ struct ShadowPolicy {
     unsigned long long n;
     uint32_t slot;             // per lane: queue entry whose sun ray this lane marches
     uint32_t head, waiting;    // FUSE, warp-uniform: the list is entries head .. head + waiting - 1 (mod kShadeList)
+    uint32_t done_ballot;      // FUSE: lanes finishing in this round (set by run_lanes before finish())
 
     __device__ __forceinline__ ShadowPolicy(const FrameParams& fp, ShadowQueue sq, uint8_t* b, int32_t* sp, uint2* l)
-        : f(fp), q(sq), bgra(b), steps_plane(sp), list(l), n(*sq.count), slot(0), head(0), waiting(0) {}
+        : f(fp), q(sq), bgra(b), steps_plane(sp), list(l), n(*sq.count), slot(0), head(0), waiting(0), done_ballot(0) {}
     __device__ __forceinline__ unsigned long long count() const { return n; }
     __device__ __forceinline__ int max_steps() const { return kMaxSteps; }
     __device__ __forceinline__ void prepare(Lane& L) { // direction and slab inverses are the same for every sun ray
@@ -413,7 +419,7 @@ struct ShadowPolicy {
     __device__ __forceinline__ void finish(const WorldView&, Lane& L, V3, uint32_t) {
         const uint32_t result = (uint32_t)L.total | ((L.flags & F_HIT) ? 0x80000000u : 0u);
         if (FUSE) {
-            const uint32_t m = __activemask(), rank = (uint32_t)__popc(m & ((1u << (threadIdx.x & 31u)) - 1u));
+            const uint32_t rank = (uint32_t)__popc(done_ballot & ((1u << (threadIdx.x & 31u)) - 1u));
             list[(head + waiting + rank) & (kShadeList - 1u)] = make_uint2(slot, result);
         } else {
             q.aux[slot + f.ids] = result;
@@ -566,6 +572,7 @@ extern "C" int vx_tracer_destroy(vx_tracer* t) {
     for (int i = 0; i < 4; ++i) if (t->slice_ev[i]) cudaEventDestroy(t->slice_ev[i]);
     if (t->copy_stream) cudaStreamDestroy(t->copy_stream);
     if (t->stream) cudaStreamDestroy(t->stream);
+    destroy_batch_pipe(t->batch);
     delete t;
     return VX_OK;
 }
@@ -652,14 +659,127 @@ extern "C" int vx_trace_device(vx_tracer* t, const float* d_origins, const float
     return launch_trace(t, d_origins, d_dirs, n, opts, out_dev, (cudaStream_t)stream);
 }
 
-extern "C" int vx_trace(vx_tracer* t, const float* origins, const float* dirs, size_t n, const vx_trace_opts* opts, const vx_hits* out) {
-    VX_REQUIRE(t && out && (n == 0 || (origins && dirs)), "NULL argument");
-    if (n > t->max_rays) { set_error("vx_trace: more rays than the tracer was created for"); return VX_ERR_CAPACITY; }
-    if (n == 0) return VX_OK;
-    DeviceGuard guard(t->device);
+// ---- batch rays in HOST arrays (VoxelRaytracer3D::Raytrace(vector, vector), VolumeRaytracer.cu:574-618) ----------------------
+// The reference copies both vectors up with blocking pageable cudaMemcpy, runs the kernel, and copies three planes down the
+// same way.  A pageable copy is a single host thread feeding the driver's staging buffers (7-10 GB/s), which for 2 M rays is
+// 20 ms around a 0.2 ms march.  Here the call is a three-stage pipeline over chunks of kBatchChunk rays: a small pool of
+// host threads copies chunk k+1's rays into a page-locked ring while the DMA engines move chunk k up and chunk k-1's planes
+// down (own streams, events between them) and the march of chunk k runs in between; only the planes the caller passed are
+// computed, moved and copied out.  Ring, pool and streams belong to the tracer and are created on the first call.
+namespace vx {
+
+constexpr size_t kBatchChunk = 256 * 1024; // rays per pipeline stage
+constexpr int kBatchSlots = 3;             // ring depth: staging in, in flight, draining
+
+struct CopyPool { // fixed set of worker threads running one sliced memcpy job at a time
+    std::vector<std::thread> workers;
+    std::mutex mu;
+    std::condition_variable cv_job, cv_done;
+    struct Part { void* dst; const void* src; size_t bytes; };
+    std::vector<Part> parts;
+    size_t next_part = 0, pending = 0;
+    unsigned long long generation = 0;
+    bool stop = false;
+
+    explicit CopyPool(int n) {
+        for (int i = 0; i < n; ++i) workers.emplace_back([this] { run(); });
+    }
+    ~CopyPool() {
+        { std::lock_guard<std::mutex> g(mu); stop = true; }
+        cv_job.notify_all();
+        for (auto& w : workers) w.join();
+    }
+    void run() {
+        std::unique_lock<std::mutex> lk(mu);
+        for (;;) {
+            cv_job.wait(lk, [this] { return stop || next_part < parts.size(); });
+            if (stop) return;
+            const Part p = parts[next_part++];
+            lk.unlock();
+            memcpy(p.dst, p.src, p.bytes);
+            lk.lock();
+            if (--pending == 0) cv_done.notify_all();
+        }
+    }
+    // copies every (dst, src, bytes) of `jobs`, each cut into slices, on the workers and the calling thread; returns when done
+    void copy(const std::vector<Part>& jobs) {
+        constexpr size_t kSlice = 256 * 1024;
+        std::unique_lock<std::mutex> lk(mu);
+        parts.clear(); next_part = 0;
+        for (const Part& j : jobs)
+            for (size_t off = 0; off < j.bytes; off += kSlice)
+                parts.push_back({(char*)j.dst + off, (const char*)j.src + off, j.bytes - off < kSlice ? j.bytes - off : kSlice});
+        pending = parts.size();
+        if (!pending) return;
+        cv_job.notify_all();
+        while (next_part < parts.size()) { // the caller works too
+            const Part p = parts[next_part++];
+            lk.unlock();
+            memcpy(p.dst, p.src, p.bytes);
+            lk.lock();
+            --pending;
+        }
+        cv_done.wait(lk, [this] { return pending == 0; });
+    }
+};
+
+struct BatchPipe {
+    CopyPool* pool = nullptr;
+    uint8_t* h_in[kBatchSlots] = {};   // pinned: origins then dirs of one chunk
+    uint8_t* h_out[kBatchSlots] = {};  // pinned: the requested planes of one chunk, back to back
+    cudaStream_t s_up = nullptr, s_run = nullptr, s_down = nullptr;
+    cudaEvent_t ev_up[kBatchSlots] = {}, ev_run[kBatchSlots] = {}, ev_down[kBatchSlots] = {};
+    ~BatchPipe() {
+        delete pool;
+        for (int i = 0; i < kBatchSlots; ++i) {
+            if (h_in[i]) cudaFreeHost(h_in[i]);
+            if (h_out[i]) cudaFreeHost(h_out[i]);
+            if (ev_up[i]) cudaEventDestroy(ev_up[i]);
+            if (ev_run[i]) cudaEventDestroy(ev_run[i]);
+            if (ev_down[i]) cudaEventDestroy(ev_down[i]);
+        }
+        if (s_up) cudaStreamDestroy(s_up);
+        if (s_run) cudaStreamDestroy(s_run);
+        if (s_down) cudaStreamDestroy(s_down);
+    }
+};
+void destroy_batch_pipe(BatchPipe* p) { delete p; }
+
+constexpr size_t kPlaneBytes[9] = {1, 12, 12, 4, 12, 4, 4, 4, 12}; // hit pos normal steps voxel brick coarse fine counters
+constexpr size_t kOutBytesPerRay = 1 + 12 + 12 + 4 + 12 + 4 + 4 + 4 + 12;
+
+static int batch_pipe(vx_tracer* t, BatchPipe** out) {
+    if (t->batch) { *out = t->batch; return VX_OK; }
+    BatchPipe* p = new BatchPipe();
+    t->batch = p; // owned by the tracer from here on (vx_tracer_destroy frees whatever was created)
+    static const int kThreads = [] {
+        const char* e = getenv("VX_BATCH_THREADS");
+        int v = e ? atoi(e) : (int)std::thread::hardware_concurrency() / 2;
+        return v < 1 ? 1 : (v > 16 ? 16 : v);
+    }();
+    p->pool = new CopyPool(kThreads - 1);
+    for (int i = 0; i < kBatchSlots; ++i) {
+        VX_CUDA(cudaHostAlloc((void**)&p->h_in[i], kBatchChunk * 24, cudaHostAllocDefault));
+        VX_CUDA(cudaHostAlloc((void**)&p->h_out[i], kBatchChunk * kOutBytesPerRay, cudaHostAllocDefault));
+        VX_CUDA(cudaEventCreateWithFlags(&p->ev_up[i], cudaEventDisableTiming));
+        VX_CUDA(cudaEventCreateWithFlags(&p->ev_run[i], cudaEventDisableTiming));
+        VX_CUDA(cudaEventCreateWithFlags(&p->ev_down[i], cudaEventDisableTiming));
+    }
+    VX_CUDA(cudaStreamCreateWithFlags(&p->s_up, cudaStreamNonBlocking));
+    VX_CUDA(cudaStreamCreateWithFlags(&p->s_run, cudaStreamNonBlocking));
+    VX_CUDA(cudaStreamCreateWithFlags(&p->s_down, cudaStreamNonBlocking));
+    *out = p;
+    return VX_OK;
+}
+
+// A handful of rays (probes, unit tests): not worth a ring — plain copies on the tracer's stream.
+constexpr size_t kBatchSmall = 32 * 1024;
+static int trace_small(vx_tracer* t, const float* origins, const float* dirs, size_t n, const vx_trace_opts* opts, const vx_hits* out) {
     cudaStream_t s = t->stream;
     VX_CUDA(cudaMemcpyAsync(t->d_origins, origins, n * 12, cudaMemcpyHostToDevice, s));
     VX_CUDA(cudaMemcpyAsync(t->d_dirs, dirs, n * 12, cudaMemcpyHostToDevice, s));
+    void* const h_plane[9] = {out->hit, out->pos, out->normal, out->steps, out->voxel, out->brick, out->coarse_steps, out->fine_steps, out->counters};
+    void* const d_plane[9] = {t->d_hit, t->d_pos, t->d_normal, t->d_steps, t->d_voxel, t->d_brick, t->d_csteps, t->d_fsteps, t->d_counters};
     vx_hits dev;
     dev.hit = out->hit ? t->d_hit : nullptr; dev.pos = out->pos ? t->d_pos : nullptr; dev.normal = out->normal ? t->d_normal : nullptr;
     dev.steps = out->steps ? t->d_steps : nullptr; dev.voxel = out->voxel ? t->d_voxel : nullptr; dev.brick = out->brick ? t->d_brick : nullptr;
@@ -667,12 +787,67 @@ extern "C" int vx_trace(vx_tracer* t, const float* origins, const float* dirs, s
     dev.counters = out->counters ? t->d_counters : nullptr;
     int rc = launch_trace(t, t->d_origins, t->d_dirs, n, opts, &dev, s);
     if (rc) return rc;
-#define VX_BACK(h, d, bytes) if (h) VX_CUDA(cudaMemcpyAsync(h, d, (bytes), cudaMemcpyDeviceToHost, s))
-    VX_BACK(out->hit, t->d_hit, n); VX_BACK(out->pos, t->d_pos, n * 12); VX_BACK(out->normal, t->d_normal, n * 12);
-    VX_BACK(out->steps, t->d_steps, n * 4); VX_BACK(out->voxel, t->d_voxel, n * 12); VX_BACK(out->brick, t->d_brick, n * 4);
-    VX_BACK(out->coarse_steps, t->d_csteps, n * 4); VX_BACK(out->fine_steps, t->d_fsteps, n * 4); VX_BACK(out->counters, t->d_counters, n * 12);
-#undef VX_BACK
+    for (int i = 0; i < 9; ++i)
+        if (h_plane[i]) VX_CUDA(cudaMemcpyAsync(h_plane[i], d_plane[i], n * kPlaneBytes[i], cudaMemcpyDeviceToHost, s));
     VX_CUDA(cudaStreamSynchronize(s));
+    return VX_OK;
+}
+
+} // namespace vx
+
+extern "C" int vx_trace(vx_tracer* t, const float* origins, const float* dirs, size_t n, const vx_trace_opts* opts, const vx_hits* out) {
+    VX_REQUIRE(t && out && (n == 0 || (origins && dirs)), "NULL argument");
+    if (n > t->max_rays) { set_error("vx_trace: more rays than the tracer was created for"); return VX_ERR_CAPACITY; }
+    if (n == 0) return VX_OK;
+    DeviceGuard guard(t->device);
+    if (n < kBatchSmall) return trace_small(t, origins, dirs, n, opts, out);
+    BatchPipe* p = nullptr;
+    int rc = batch_pipe(t, &p);
+    if (rc) return rc;
+    void* const h_plane[9] = {out->hit, out->pos, out->normal, out->steps, out->voxel, out->brick, out->coarse_steps, out->fine_steps, out->counters};
+    void* const d_plane[9] = {t->d_hit, t->d_pos, t->d_normal, t->d_steps, t->d_voxel, t->d_brick, t->d_csteps, t->d_fsteps, t->d_counters};
+    const size_t chunks = (n + kBatchChunk - 1) / kBatchChunk;
+    auto count_of = [&](size_t k) { return k + 1 < chunks ? kBatchChunk : n - k * kBatchChunk; };
+    // drain(k): chunk k's planes from the ring into the caller's arrays
+    auto drain = [&](size_t k) -> int {
+        const int slot = (int)(k % kBatchSlots);
+        const size_t first = k * kBatchChunk, cnt = count_of(k);
+        VX_CUDA(cudaEventSynchronize(p->ev_down[slot]));
+        std::vector<CopyPool::Part> jobs;
+        size_t off = 0;
+        for (int i = 0; i < 9; ++i)
+            if (h_plane[i]) { jobs.push_back({(char*)h_plane[i] + first * kPlaneBytes[i], p->h_out[slot] + off, cnt * kPlaneBytes[i]}); off += cnt * kPlaneBytes[i]; }
+        p->pool->copy(jobs);
+        return VX_OK;
+    };
+    for (size_t k = 0; k < chunks; ++k) {
+        const int slot = (int)(k % kBatchSlots);
+        const size_t first = k * kBatchChunk, cnt = count_of(k);
+        if (k >= (size_t)kBatchSlots) { rc = drain(k - kBatchSlots); if (rc) return rc; } // frees this slot's halves of the ring
+        p->pool->copy({{p->h_in[slot], origins + 3 * first, cnt * 12}, {p->h_in[slot] + cnt * 12, dirs + 3 * first, cnt * 12}});
+        VX_CUDA(cudaMemcpyAsync(t->d_origins + 3 * first, p->h_in[slot], cnt * 12, cudaMemcpyHostToDevice, p->s_up));
+        VX_CUDA(cudaMemcpyAsync(t->d_dirs + 3 * first, p->h_in[slot] + cnt * 12, cnt * 12, cudaMemcpyHostToDevice, p->s_up));
+        VX_CUDA(cudaEventRecord(p->ev_up[slot], p->s_up));
+        VX_CUDA(cudaStreamWaitEvent(p->s_run, p->ev_up[slot], 0));
+        vx_hits dev;
+        dev.hit = out->hit ? t->d_hit + first : nullptr; dev.pos = out->pos ? t->d_pos + 3 * first : nullptr;
+        dev.normal = out->normal ? t->d_normal + 3 * first : nullptr; dev.steps = out->steps ? t->d_steps + first : nullptr;
+        dev.voxel = out->voxel ? t->d_voxel + 3 * first : nullptr; dev.brick = out->brick ? t->d_brick + first : nullptr;
+        dev.coarse_steps = out->coarse_steps ? t->d_csteps + first : nullptr; dev.fine_steps = out->fine_steps ? t->d_fsteps + first : nullptr;
+        dev.counters = out->counters ? t->d_counters + 3 * first : nullptr;
+        rc = launch_trace(t, t->d_origins + 3 * first, t->d_dirs + 3 * first, cnt, opts, &dev, p->s_run);
+        if (rc) return rc;
+        VX_CUDA(cudaEventRecord(p->ev_run[slot], p->s_run));
+        VX_CUDA(cudaStreamWaitEvent(p->s_down, p->ev_run[slot], 0));
+        size_t off = 0;
+        for (int i = 0; i < 9; ++i)
+            if (h_plane[i]) {
+                VX_CUDA(cudaMemcpyAsync(p->h_out[slot] + off, (const char*)d_plane[i] + first * kPlaneBytes[i], cnt * kPlaneBytes[i], cudaMemcpyDeviceToHost, p->s_down));
+                off += cnt * kPlaneBytes[i];
+            }
+        VX_CUDA(cudaEventRecord(p->ev_down[slot], p->s_down));
+    }
+    for (size_t k = chunks > (size_t)kBatchSlots ? chunks - kBatchSlots : 0; k < chunks; ++k) { rc = drain(k); if (rc) return rc; }
     return VX_OK;
 }
 

@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(256) analyse_bricks(const uint32_t* __restrict
                                                       uint32_t* __restrict__ top, unsigned long long* __restrict__ solid,
                                                       BuildGeom g, uint32_t nbricks) {
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t brick = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t brick = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5); // 64-bit: nbricks * 32 passes 2^32 at 2^27 bricks
     if (brick >= nbricks) return;
     const uint32_t words = g.tpb * 16u;
     int mnx = 255, mny = 255, mnz = 255, mxx = -1, mxy = -1, mxz = -1;
@@ -269,6 +269,36 @@ __global__ void export_bricks(const uint2* __restrict__ precords, const uint32_t
     }
 }
 
+// the same for a list of bricks given by coarse coordinates (parity spot checks on worlds too large to export whole)
+__global__ void export_selected(const uint2* __restrict__ precords, const uint32_t* __restrict__ ptop, const uint32_t* __restrict__ top,
+                                const uint32_t* __restrict__ pool, uint32_t words, const uint32_t* __restrict__ coords, uint32_t n, BuildGeom g,
+                                uint8_t* __restrict__ occupied, uint32_t* __restrict__ brick_words, float* __restrict__ bounds6) {
+    const uint32_t i = blockIdx.x;
+    if (i >= n) return;
+    const uint32_t bx = coords[3 * i], by = coords[3 * i + 1], bz = coords[3 * i + 2];
+    const uint64_t p = ((uint64_t)(bz + 1u) * (g.cy + 2u) + (by + 1u)) * (g.cx + 2u) + (bx + 1u);
+    const bool occ = (ptop[p >> 5] >> (p & 31u)) & 1u;
+    const uint2 rec = precords[p];
+    if (occupied && threadIdx.x == 0) {
+        // both copies of the top-level bit: the traversal grid's and the reference-indexed one (bit 1)
+        const uint64_t t = (uint64_t)((bx >> 3) + (by >> 3) * (g.cx >> 3) + (bz >> 3) * (g.cx >> 3) * (g.cy >> 3)) * 512u + (bx & 7u) + ((by & 7u) << 3) + ((bz & 7u) << 6);
+        occupied[i] = (uint8_t)((occ ? 1u : 0u) | (((top[t >> 5] >> (t & 31u)) & 1u) << 1));
+    }
+    if (brick_words)
+        for (uint32_t k = threadIdx.x; k < words; k += blockDim.x)
+            brick_words[(uint64_t)i * words + k] = occ ? pool[(uint64_t)rec.y * words + k] : 0u;
+    if (bounds6 && threadIdx.x == 0) {
+        float* o = bounds6 + (uint64_t)i * 6u;
+        if (occ) {
+            const uint32_t b = rec.x;
+            o[0] = (float)(b & 31u); o[1] = (float)((b >> 5) & 31u); o[2] = (float)((b >> 10) & 31u);
+            o[3] = (float)((b >> 15) & 31u); o[4] = (float)((b >> 20) & 31u); o[5] = (float)((b >> 25) & 31u);
+        } else {
+            o[0] = o[1] = o[2] = 0.0f; o[3] = o[4] = o[5] = -1.0f;
+        }
+    }
+}
+
 } // namespace vx
 
 // =============================================================================================
@@ -366,12 +396,13 @@ static int build_common(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int 
     const uint64_t ntiles = w->nbricks * g.tpb;
     uint32_t* d_tmp = nullptr;
     uint32_t* d_dense = nullptr;
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    auto cleanup = [&]() { cudaFree(d_tmp); cudaFree(d_dense); if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); };
+    cudaEvent_t e0 = nullptr, e1 = nullptr, em = nullptr;
+    auto cleanup = [&]() { cudaFree(d_tmp); cudaFree(d_dense); if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); if (em) cudaEventDestroy(em); };
 #define VX_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); free_world(w); return cuda_fail(e_, #call, __FILE__, __LINE__); } } while (0)
     VX_TRY(cudaMalloc(&d_tmp, (size_t)ntiles * 64));
     VX_TRY(cudaEventCreate(&e0));
     VX_TRY(cudaEventCreate(&e1));
+    VX_TRY(cudaEventCreate(&em));
     if (host_dense) {
         VX_TRY(cudaMalloc(&d_dense, (size_t)ntiles * 64));
         VX_TRY(cudaMemcpy(d_dense, host_dense, (size_t)ntiles * 64, cudaMemcpyHostToDevice));
@@ -388,11 +419,13 @@ static int build_common(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int 
         else noise_tiles<true><<<blocks, 256>>>(d_tmp, g, ntiles);
     }
     VX_TRY(cudaGetLastError());
+    VX_TRY(cudaEventRecord(em));
     rc = finish_build(w, d_tmp, g);
     if (rc) { cleanup(); free_world(w); return rc; }
     VX_TRY(cudaEventRecord(e1));
     VX_TRY(cudaEventSynchronize(e1));
     VX_TRY(cudaEventElapsedTime(&w->build_ms, e0, e1));
+    VX_TRY(cudaEventElapsedTime(&w->tiles_ms, e0, em));
 #undef VX_TRY
     cleanup();
     *out = w;
@@ -442,6 +475,7 @@ extern "C" int vx_world_get_info(const vx_world* w, vx_world_info* info) {
     info->bytes_top = (w->nbricks + 31) / 32 * 4 + ((uint64_t)(w->cx + 2) * (w->cy + 2) * (w->cz + 2) + 31) / 32 * 4; info->bytes_records = (uint64_t)(w->cx + 2) * (w->cy + 2) * (w->cz + 2) * 8;
     info->bytes_pool = w->occupied * w->words_per_brick * 4;
     info->build_ms = w->build_ms;
+    info->tiles_ms = w->tiles_ms;
     return VX_OK;
 }
 extern "C" int vx_world_download(const vx_world* w, uint32_t* top_words, uint32_t* brick_words, float* bounds6) {
@@ -461,5 +495,33 @@ extern "C" int vx_world_download(const vx_world* w, uint32_t* top_words, uint32_
         if (bounds6) VX_CUDA(cudaMemcpy(bounds6, d_b6, (size_t)nb * 24, cudaMemcpyDeviceToHost));
         cudaFree(d_bw); cudaFree(d_b6);
     }
+    return VX_OK;
+}
+
+extern "C" int vx_world_download_bricks(const vx_world* w, const uint32_t* coarse_xyz, size_t n, uint8_t* occupied, uint32_t* brick_words,
+                                        float* bounds6) {
+    VX_REQUIRE(w && (coarse_xyz || n == 0), "NULL argument");
+    VX_REQUIRE(n < (1ull << 31), "too many bricks in one call");
+    if (n == 0) return VX_OK;
+    for (size_t i = 0; i < n; ++i)
+        VX_REQUIRE(coarse_xyz[3 * i] < w->cx && coarse_xyz[3 * i + 1] < w->cy && coarse_xyz[3 * i + 2] < w->cz, "brick coordinates outside the coarse grid");
+    DeviceGuard guard(w->device);
+    uint32_t* d_xyz = nullptr; uint8_t* d_occ = nullptr; uint32_t* d_bw = nullptr; float* d_b6 = nullptr;
+    auto cleanup = [&]() { cudaFree(d_xyz); cudaFree(d_occ); cudaFree(d_bw); cudaFree(d_b6); };
+#define VX_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return cuda_fail(e_, #call, __FILE__, __LINE__); } } while (0)
+    VX_TRY(cudaMalloc(&d_xyz, n * 12));
+    VX_TRY(cudaMemcpy(d_xyz, coarse_xyz, n * 12, cudaMemcpyHostToDevice));
+    if (occupied) VX_TRY(cudaMalloc(&d_occ, n));
+    if (brick_words) VX_TRY(cudaMalloc(&d_bw, n * w->words_per_brick * 4));
+    if (bounds6) VX_TRY(cudaMalloc(&d_b6, n * 24));
+    BuildGeom g{};
+    g.cx = w->cx; g.cy = w->cy; g.cz = w->cz; g.f8 = w->factor / 8; g.tpb = g.f8 * g.f8 * g.f8;
+    export_selected<<<(uint32_t)n, 32>>>(w->d_precords, w->d_ptop, w->d_top, w->d_pool, w->words_per_brick, d_xyz, (uint32_t)n, g, d_occ, d_bw, d_b6);
+    VX_TRY(cudaGetLastError());
+    if (occupied) VX_TRY(cudaMemcpy(occupied, d_occ, n, cudaMemcpyDeviceToHost));
+    if (brick_words) VX_TRY(cudaMemcpy(brick_words, d_bw, n * w->words_per_brick * 4, cudaMemcpyDeviceToHost));
+    if (bounds6) VX_TRY(cudaMemcpy(bounds6, d_b6, n * 24, cudaMemcpyDeviceToHost));
+#undef VX_TRY
+    cleanup();
     return VX_OK;
 }

@@ -17,9 +17,16 @@ BAND_ROWS = 8  # rows per band: one 16x8 macro tile row of the primary-ray kerne
 
 
 class FramePartition:
-    def __init__(self, W, H, world_size, rank, bytes_per_pixel=4):
+    """`checkerboard`: the frames are rendered with vx_render_opts.checkerboard = 1 (the reference's default,
+    Renderer.cu:186-194).  A band is 8 rows of THREADS; with the checkerboard mapping y = 2 * ty + {0, 1, 2} it covers
+    pixel rows 16 b .. 16 b + 17, overlapping the next band's, so a rank's pixels are not whole pixel rows and cannot be
+    moved by row copies: gather(), render_and_gather() and HostFrame refuse such a partition.  SharedFrame (every rank's
+    kernels store their own pixels into the one frame) is exact for checkerboard frames and is the path to use."""
+
+    def __init__(self, W, H, world_size, rank, bytes_per_pixel=4, checkerboard=False):
         if not (0 <= rank < world_size):
             raise ValueError("rank %d outside world of %d" % (rank, world_size))
+        self.checkerboard = bool(checkerboard)
         self.W, self.H, self.world_size, self.rank = W, H, world_size, rank
         self.bands = (H + BAND_ROWS - 1) // BAND_ROWS
         self.band_bytes = BAND_ROWS * W * bytes_per_pixel
@@ -65,6 +72,7 @@ class FramePartition:
         """Pipelined frame: for every row chunk call render_rows(y0, rows) (which must enqueue this rank's render of
         those rows on the current stream / do it synchronously on CPU), then start the gather of that chunk's bands
         asynchronously, so the transfer of one chunk overlaps the render of the next.  Collective."""
+        self._require_row_bands("render_and_gather")
         if self.world_size == 1:
             render_rows(0, self.H)
             return frame
@@ -97,8 +105,14 @@ class FramePartition:
     def _views(self, frame):
         return frame.view(self.bands, self.band_bytes)
 
+    def _require_row_bands(self, what):
+        if self.checkerboard and self.world_size > 1:
+            raise ValueError("%s moves whole pixel rows, but the bands of a checkerboard frame interleave "
+                             "(thread row ty writes pixel rows 2 ty .. 2 ty + 2): use SharedFrame, or render without checkerboard" % what)
+
     def gather(self, frame, group=None):
         """Collect every rank's bands into rank 0's `frame` (a flat uint8 tensor of frame_bytes()).  Collective."""
+        self._require_row_bands("gather")
         if self.world_size == 1:
             return frame
         fb = self._views(frame)
@@ -220,6 +234,7 @@ class HostFrame:
         import ctypes
         import numpy as np
         import voxelengine_b200 as vx
+        part._require_row_bands("HostFrame")
         self._vx, self.part, self.device, self.group = vx, part, device, group
         self.nbytes = part.frame_bytes()
         box = [None]
