@@ -4,7 +4,12 @@ usage: python tools/hot_sass.py file.csv [min_share_percent]"""
 import csv, sys
 rows = list(csv.reader(open(sys.argv[1])))
 thr = float(sys.argv[2]) if len(sys.argv) > 2 else 0.5
-hdr = rows[1]; data = rows[2:]
+hdr = rows[1]
+data = []
+for r in rows[2:]:  # one block per kernel instance in the report: keep the first
+    if len(r) != len(hdr): break
+    if r[:2] == hdr[:2]: break
+    data.append(r)
 iS = hdr.index('Source'); iI = hdr.index('Instructions Executed'); iT = hdr.index('Thread Instructions Executed'); iSm = hdr.index('# Samples')
 tot = sum(int(r[iI]) for r in data); tots = sum(int(r[iSm]) for r in data)
 print('total warp-inst', tot, 'samples', tots, 'sass lines', len(data))

@@ -338,6 +338,155 @@ done:
     o.ncode = axis == 3u ? 0u : (axis == 2u ? (oz ? 5u : 6u) : (axis == 1u ? (oy ? 3u : 4u) : (ox ? 1u : 2u)));
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// The brick march again, with everything that is not needed to FIND the end of the march taken out of the loop.
+// What the reference's loop does per voxel (VolumeRaytracer.cu:236-349): range test, voxel lookup, axis choice, crossing
+// point, test of the crossing point against [0,8]^3, step count, point and normal.  What decides where the march ends is
+// only the lookup, the axis choice (the tMax values, accumulated with the same float additions) and the cell leaving the
+// brick; the rest is recovered afterwards:
+//   * the cell is a 9-bit voxel index plus one nibble per axis; leaving the brick sets bit 3 of a nibble (one AND tests all three);
+//   * the step count is the sum of what the nibbles gained, the last axis is the nibble that moved last, and the crossing
+//     point of the last counted step is rebuilt from its t (the smallest tMax of that round, which the loop keeps);
+//   * the crossing-point test: on the stepped axis the coordinate is a voxel face (an integer in [0,8]: passes); on the
+//     other axes it is fl(s + fl(t * d)), which is monotone in t, so over the whole march it stays between its values at
+//     the first and the last crossing.  Those two are evaluated after the loop for all three axes (which is at least what
+//     the reference tests); if any of the six lies outside [0,8] — a ray within rounding of a brick face, about one march
+//     in a thousand — the function gives up and the caller runs the statement-by-statement march instead.
+//   * a march that starts ON the far face of the brick (cell coordinate 8: IsOnEdge, :216-232 — every second entry through
+//     a +x/+y/+z face, since the entry point is rounded) takes its first step out of the virtual cell before the loop when
+//     that step is the first one the rule picks; every other combination (two such axes, another axis first) is left
+//     to the caller's generic march.
+// Returns false when the caller must run fine_march<true>() instead (nothing has been written to `o` then).
+// 23 SASS per voxel step instead of 62.
+// ---------------------------------------------------------------------------------------------------------------------
+// The loop works in MIRRORED brick coordinates c' = (d > 0 ? c : 7 - c), in which every ray moves towards +x', +y', +z':
+// the increments are the constants 1 / 8 / 64 (voxel index) and 1 / 16 / 256 (the per-axis cell nibbles, whose bit 3 comes
+// on when a cell coordinate reaches 8, i.e. leaves the brick), whatever the direction, and the real voxel index is the
+// mirrored one XOR a per-ray constant (7 - c == c ^ 7 on three bits).
+constexpr uint32_t kFineOut = 0x888u;
+#ifdef VX_FINE_STATS // diagnostics build (tools/build_variants.sh): how often the quick march hands over to the generic one, and why
+__device__ unsigned long long g_fine_stats[8];
+#define VX_FSTAT(i) atomicAdd(&g_fine_stats[i], 1ull)
+#else
+#define VX_FSTAT(i) ((void)0)
+#endif
+
+__device__ __forceinline__ void fine_step(float& tx, float& ty, float& tz, uint32_t& bit, uint32_t& u, float& t, float dtx, float dty, float dtz) {
+    asm("{\n\t.reg .pred pz, py, px;\n\t"
+        "min.f32 %5, %0, %1, %2;\n\t"                // t of this crossing: the smallest tMax
+        "setp.le.f32 pz, %2, %5;\n\t"                // ties: z over y over x (:293-322 without NaNs)
+        "setp.le.and.f32 py|px, %1, %5, !pz;\n\t"
+        "@pz add.rn.f32 %2, %2, %8;\n\t"
+        "@py add.rn.f32 %1, %1, %7;\n\t"
+        "@px add.rn.f32 %0, %0, %6;\n\t"
+        "@pz add.s32 %3, %3, 64;\n\t"
+        "@py add.s32 %3, %3, 8;\n\t"
+        "@px add.s32 %3, %3, 1;\n\t"
+        "@pz add.s32 %4, %4, 256;\n\t"
+        "@py add.s32 %4, %4, 16;\n\t"
+        "@px add.s32 %4, %4, 1;\n\t}"
+        : "+f"(tx), "+f"(ty), "+f"(tz), "+r"(bit), "+r"(u), "=f"(t)
+        : "f"(dtx), "f"(dty), "f"(dtz));
+}
+
+__device__ __forceinline__ bool fine_march8_quick(const uint32_t* __restrict__ mask, V3 s, const Ray& r, FineOut& o) {
+    int cx = (int)s.x, cy = (int)s.y, cz = (int)s.z;
+    if ((unsigned)cx > 8u || (unsigned)cy > 8u || (unsigned)cz > 8u) { VX_FSTAT(1); return false; }
+    const int ox = r.sx > 0, oy = r.sy > 0, oz = r.sz > 0;
+    float tx = r.d.x != 0.0f ? fdiv(fsub((float)(cx + ox), s.x), r.d.x) : CUDART_INF_F;
+    float ty = r.d.y != 0.0f ? fdiv(fsub((float)(cy + oy), s.y), r.d.y) : CUDART_INF_F;
+    float tz = r.d.z != 0.0f ? fdiv(fsub((float)(cz + oz), s.z), r.d.z) : CUDART_INF_F;
+    VX_FSTAT(0);
+    const float t_first = fminf(fminf(tx, ty), tz);
+    int pre = 0; // steps taken before the loop (out of a virtual cell on the far face)
+    const uint32_t edge = (cx == 8 ? 1u : 0u) | (cy == 8 ? 2u : 0u) | (cz == 8 ? 4u : 0u);
+    if (edge) {
+        // an axis that sits on the far face and does not descend: the cell is outside at once (:216-232, :283-287)
+        if ((cx == 8 && !(r.d.x < 0.0f)) || (cy == 8 && !(r.d.y < 0.0f)) || (cz == 8 && !(r.d.z < 0.0f))) {
+            o.hit = false; o.oob = true; o.cell = 0; o.point = s; o.steps = 0; o.ncode = 0;
+            return true;
+        }
+        VX_FSTAT(5);
+        if (edge & (edge - 1u)) { VX_FSTAT(2); return false; } // two axes on their far faces: generic march
+        const bool pz = tz <= fminf(tx, ty), py = !pz && ty <= tx;
+        const uint32_t first = pz ? 4u : (py ? 2u : 1u);
+        if (first != edge) { VX_FSTAT(3); return false; }      // another axis moves first: generic march
+        // the virtual cell looks up the clamped voxel (:240-246); then the first step leaves it through the face at 8
+        cx = min(cx, 7); cy = min(cy, 7); cz = min(cz, 7);
+        if (cell_bit(mask, (uint32_t)(cx + (cy << 3) + (cz << 6)))) {
+            o.hit = true; o.oob = false; o.steps = 0; o.point = s; o.ncode = 0;
+            o.cell = (uint32_t)cx | ((uint32_t)cy << 10) | ((uint32_t)cz << 20);
+            return true;
+        }
+        if (edge == 1u) tx = fadd(tx, r.dtx); else if (edge == 2u) ty = fadd(ty, r.dty); else tz = fadd(tz, r.dtz);
+        pre = 1;
+    }
+    const uint32_t mx = (uint32_t)(ox ? cx : 7 - cx), my = (uint32_t)(oy ? cy : 7 - cy), mz = (uint32_t)(oz ? cz : 7 - cz); // mirrored cell
+    const uint32_t flip = (ox ? 0u : 7u) | (oy ? 0u : 56u) | (oz ? 0u : 448u);
+    const uint32_t u0 = mx | (my << 4) | (mz << 8);
+    uint32_t u = u0, up = u0;
+    uint32_t bit = mx + (my << 3) + (mz << 6);
+    float t_last = t_first, t_prev = t_first; // t of the last crossing and of the one before it
+    float dtx = r.dtx, dty = r.dty, dtz = r.dtz;
+    // keep the loop invariants in registers: left alone, ptxas re-derives the mask address and the deltas in every round
+    asm volatile("" : "+f"(dtx), "+f"(dty), "+f"(dtz), "+l"(mask));
+    bool hit;
+#pragma unroll 1
+    for (;;) {
+        hit = cell_bit(mask, bit ^ flip);
+        if (hit) break;
+        up = u; t_prev = t_last;
+        fine_step(tx, ty, tz, bit, u, t_last, dtx, dty, dtz);
+        if (u & kFineOut) break;
+    }
+    const int steps = pre + (int)((u & 15u) + ((u >> 4) & 15u) + (u >> 8)) - (int)((u0 & 15u) + ((u0 >> 4) & 15u) + (u0 >> 8));
+    if (steps == 0) { // the first voxel is solid
+        o.hit = true; o.oob = false; o.steps = 0; o.point = s; o.ncode = 0;
+        o.cell = (uint32_t)cx | ((uint32_t)cy << 10) | ((uint32_t)cz << 20);
+        return true;
+    }
+    // the last counted step: the axis whose nibble moved last (the step out of the virtual cell when the loop took none)
+    const uint32_t moved = u - up;
+    const uint32_t axis = (u == u0) ? (edge == 1u ? 0u : (edge == 2u ? 1u : 2u)) : (moved == 1u ? 0u : (moved == 16u ? 1u : 2u));
+    // crossing-point test (:325-341), see above.  Crossing k steps axis a_k at t_k and tests fl(s + fl(t_k * d)) on the other
+    // two axes.  Checked here: the last crossing exactly as the reference tests it; the first crossing on all three axes
+    // (when the march goes on after it, its stepped coordinate is an interior face, far from 0 and 8).  By monotonicity in t
+    // that covers every crossing in between for the two axes that are not stepped last.  The axis stepped last is tested
+    // by the reference only at earlier crossings, all at t <= t_prev: if its value at t_last is outside [0,8] (about every
+    // second march that leaves the brick: the exit face, rounded) its value at t_prev bounds them instead.
+    const float ax = fadd(s.x, fmul(t_first, r.d.x)), ay = fadd(s.y, fmul(t_first, r.d.y)), az = fadd(s.z, fmul(t_first, r.d.z));
+    const float bx = fadd(s.x, fmul(t_last, r.d.x)), by = fadd(s.y, fmul(t_last, r.d.y)), bz = fadd(s.z, fmul(t_last, r.d.z));
+    bool bad;
+    {
+        const float lo_b = fminf(axis == 0u ? 4.0f : bx, fminf(axis == 1u ? 4.0f : by, axis == 2u ? 4.0f : bz));
+        const float hi_b = fmaxf(axis == 0u ? 4.0f : bx, fmaxf(axis == 1u ? 4.0f : by, axis == 2u ? 4.0f : bz));
+        bad = lo_b < 0.0f || hi_b > 8.0f;
+        if (steps > 1) {
+            bad = bad || fminf(fminf(ax, ay), az) < 0.0f || fmaxf(fmaxf(ax, ay), az) > 8.0f;
+            const float own = axis == 0u ? bx : (axis == 1u ? by : bz);
+            if (own < 0.0f || own > 8.0f) {
+                const float sa = axis == 0u ? s.x : (axis == 1u ? s.y : s.z), da = axis == 0u ? r.d.x : (axis == 1u ? r.d.y : r.d.z);
+                const float v = fadd(sa, fmul(t_prev, da));
+                bad = bad || v < 0.0f || v > 8.0f;
+            }
+        }
+    }
+    if (bad) { VX_FSTAT(4); return false; }
+    // final cell: un-mirror the nibbles (8 = left the brick on that axis: cell 8 or -1)
+    const int nx = (int)(u & 15u), ny = (int)((u >> 4) & 15u), nz = (int)(u >> 8);
+    const int fx = ox ? nx : 7 - nx, fy = oy ? ny : 7 - ny, fz = oz ? nz : 7 - nz;
+    // its crossing point: start + t * direction, except on the stepped axis, where it is the face of the cell that was left
+    V3 p = mk(bx, by, bz);
+    if (u == u0) { if (axis == 0u) p.x = 8.0f; else if (axis == 1u) p.y = 8.0f; else p.z = 8.0f; } // only the step out of the virtual cell
+    else if (axis == 0u) p.x = (float)(ox ? fx : fx + 1);
+    else if (axis == 1u) p.y = (float)(oy ? fy : fy + 1);
+    else p.z = (float)(oz ? fz : fz + 1);
+    o.hit = hit; o.oob = !hit; o.steps = steps; o.point = p;
+    o.cell = hit ? ((uint32_t)fx | ((uint32_t)fy << 10) | ((uint32_t)fz << 20)) : 0u;
+    o.ncode = axis == 2u ? (oz ? 5u : 6u) : (axis == 1u ? (oy ? 3u : 4u) : (ox ? 1u : 2u));
+    return true;
+}
+
 // What Raytrace does with the outcome of one brick march (VolumeRaytracer.cu:409-523): a hit ends the ray (ST_DONE + F_HIT,
 // result in pos/ncode); otherwise the start is re-seeded at the exit point with the reference's nudging rules (:438-489)
 // and the lane begins a new coarse traversal.  (qx,qy,qz) = the brick, (cx,cy,cz) = the traversal cell it was found in.
@@ -439,8 +588,12 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
     const uint32_t* mask = w.pool + (size_t)rec.y * w.words_per_brick;
     if (w.factor == 8) {
         // the tight variant whenever nothing can be NaN (the generic one keeps the reference's comparison order for NaNs)
+#ifdef VX_FINE_OLD
         if (L.flags & F_CAPOK) fine_march8(mask, local, r, q);
         else fine_march<true>(mask, 8, local, r, q);
+#else
+        if (!((L.flags & F_CAPOK) && fine_march8_quick(mask, local, r, q))) fine_march<true>(mask, 8, local, r, q);
+#endif
     } else fine_march<false>(mask, w.factor, local, r, q);
     brick_done<BATCH>(w, L, q, qx, qy, qz, cx, cy, cz, next_axis, q.steps == 0 ? sl.ncode : q.ncode, pos, ncode);
 }

@@ -1190,3 +1190,16 @@ extern "C" int vx_measure_read_bandwidth(int device, size_t bytes, int reps, flo
     *gb_per_s = best;
     return VX_OK;
 }
+
+#ifdef VX_FINE_STATS
+// diagnostics build only: [0] quick marches started, [1] start cell out of range, [2] two far faces, [3] far face not first,
+// [4] crossing test inconclusive, [5] starts on a far face; reading resets the counters
+extern "C" int vx_debug_fine_stats(unsigned long long out[8], int device) {
+    DeviceGuard guard(device);
+    VX_CUDA(cudaDeviceSynchronize());
+    VX_CUDA(cudaMemcpyFromSymbol(out, vx::g_fine_stats, 64));
+    unsigned long long zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    VX_CUDA(cudaMemcpyToSymbol(vx::g_fine_stats, zero, 64));
+    return VX_OK;
+}
+#endif
