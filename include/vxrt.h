@@ -68,6 +68,28 @@ int vx_world_destroy(vx_world* w);
 int vx_world_build_noise_full(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int factor,
                               uint32_t x0, uint32_t y0, uint32_t z0, int device);
 
+/* Partitioned build (BASELINE configs[4]; no reference counterpart: CreateVoxels builds on one GPU).  The coarse
+ * grid's 8-cell z-tiles are dealt to slab_count builders in contiguous runs; builder slab_index runs the voxel kernel and the
+ * brick analysis on its slab only.  A slab's parts — top-level bits (brick_count / 32 words), packed bounds (one uint32 per
+ * brick) and compact mask pool (occupied_bricks * words_per_brick words) — are contiguous pieces of the whole world's arrays
+ * in brick order: vx_slab_export copies them to DEVICE buffers of the caller, the caller moves them between the devices
+ * (torch.distributed / NCCL all-gather in voxelengine_b200/partition.py), and vx_world_from_parts turns the concatenation
+ * (device pointers on `device`) into a world that is word for word the one vx_world_build_noise builds. */
+typedef struct vx_slab vx_slab;
+typedef struct vx_slab_info {
+    uint64_t brick_begin, brick_count;  /* the slab's range in the reference's tiled coarse index */
+    uint64_t occupied_bricks, solid_voxels;
+    uint32_t words_per_brick;
+    float build_ms;
+} vx_slab_info;
+int vx_slab_build_noise(vx_slab** out, uint32_t X, uint32_t Y, uint32_t Z, int factor, uint32_t x0, uint32_t y0, uint32_t z0,
+                        uint32_t slab_index, uint32_t slab_count, int device);
+int vx_slab_get_info(const vx_slab* s, vx_slab_info* info);
+int vx_slab_export(const vx_slab* s, uint32_t* d_top_words, uint32_t* d_bounds, uint32_t* d_pool_words, void* stream);
+int vx_slab_destroy(vx_slab* s);
+int vx_world_from_parts(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int factor, const uint32_t* d_top_words,
+                        const uint32_t* d_bounds, const uint32_t* d_pool_words, uint64_t occupied_bricks, uint64_t solid_voxels, int device);
+
 typedef struct vx_world_info {
     uint32_t dims[3];        /* voxels */
     uint32_t coarse[3];      /* bricks */

@@ -156,3 +156,36 @@ def test_scripted_viewer_runs_and_fills_the_checkerboard(vx, tmp_path):
     assert frames[0] != frames[1]      # the second frame writes the other half of the pixels
     assert frames[1] == frames[2]      # camera at rest: the third frame rewrites the first half with the same values
     assert frames[3] != frames[2]      # the camera moved
+
+
+# ---- the frame loop on N GPUs in one process, plain C++ over the C ABI (examples/multi_gpu_main.cu) ----
+MULTI = os.path.join(ROOT, "examples", "multi_gpu")
+
+
+def build_multi():
+    subprocess.check_call(["nvcc", "-std=c++17", "-arch=sm_100a", "-w", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "multi_gpu_main.cu"), "-L" + os.path.join(ROOT, "voxelengine_b200", "lib"), "-lvxrt",
+                           "-Xlinker", "-rpath=" + os.path.join(ROOT, "voxelengine_b200", "lib"), "-o", MULTI])
+
+
+@pytest.mark.skipif(shutil.which("nvcc") is None, reason="nvcc not available")
+def test_multi_gpu_driver_compiles(vx):
+    build_multi()
+    assert os.path.exists(MULTI)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("devices", ["0", "0,0", "0,0,0", "0,1", "0,1,2,3"])
+def test_multi_gpu_driver_assembles_the_single_gpu_frame(vx, tmp_path, devices):
+    """One process, N devices (or N band sets on one device), every device's kernels storing its bands into the first
+    device's frame: the assembled frame must be the whole-frame render of one device, byte for byte (the program compares
+    them itself and returns 3 otherwise)."""
+    if max(int(d) for d in devices.split(",")) >= vx.device_count():
+        pytest.skip("needs %d GPUs" % (max(int(d) for d in devices.split(",")) + 1))
+    if not os.path.exists(MULTI):
+        build_multi()
+    out = subprocess.run([MULTI, "--devices", devices, "--world", "256", "128", "256", "--frame", "640", "360", "--frames", "3",
+                          "--out", str(tmp_path / "frame.bgra")], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout[-1000:] + out.stderr[-1000:]
+    assert "frame_identical=1" in out.stdout
+    assert os.path.getsize(tmp_path / "frame.bgra") == 640 * 360 * 4

@@ -391,3 +391,42 @@ def test_batch_call_pipeline_planes_and_ragged_chunks(vx, gpu_worlds):
     for k in INT_PLANES:
         assert np.array_equal(again[k], full[k][:1000])
     rt.close()
+
+
+@pytest.mark.parametrize("case", [((256, 128, 256), (512, 0, 256), 8, 3), ((128, 128, 256), (100, 40, 900), 16, 2), ((64, 64, 64), (0, 0, 0), 8, 4)])
+def test_partitioned_build_equals_single_device_build(vx, case):
+    """BASELINE configs[4]: the world built slab by slab (vx_slab_build_noise, here all slabs on one device, one after the
+    other) and assembled from the concatenated parts (vx_world_from_parts) is word for word the world of one
+    vx_world_build_noise — top-level bits, masks, bounds, counters — and traces the same (more builders than z-tiles
+    leaves some slabs empty: the last case)."""
+    import torch
+    dims, org, factor, n = case
+    whole = vx.World.from_noise(*dims, factor, origin=org)
+    nb = (dims[0] // factor) * (dims[1] // factor) * (dims[2] // factor)
+    wpb = factor ** 3 // 32
+    slabs = [vx.Slab(*dims, factor, r, n, origin=org) for r in range(n)]
+    infos = [s.info for s in slabs]
+    assert [int(i.brick_begin) for i in infos] == [sum(int(j.brick_count) for j in infos[:r]) for r in range(n)]
+    assert sum(int(i.brick_count) for i in infos) == nb
+    occupied = sum(int(i.occupied_bricks) for i in infos)
+    top = torch.zeros(nb // 32, dtype=torch.int32, device="cuda")
+    bounds = torch.zeros(nb, dtype=torch.int32, device="cuda")
+    pool = torch.zeros(max(occupied, 1) * wpb, dtype=torch.int32, device="cuda")
+    slot = 0
+    for s, i in zip(slabs, infos):
+        b0, bn, occ = int(i.brick_begin), int(i.brick_count), int(i.occupied_bricks)
+        if bn:
+            s.export(top[b0 // 32:].data_ptr(), bounds[b0:].data_ptr(), pool[slot * wpb:].data_ptr() if occ else 0)
+        slot += occ
+        s.close()
+    torch.cuda.synchronize()
+    parts = vx.World.from_parts(*dims, factor, top.data_ptr(), bounds.data_ptr(), pool.data_ptr(), occupied, sum(int(i.solid_voxels) for i in infos))
+    for a, b in zip(whole.download(), parts.download()):
+        assert np.array_equal(a, b)
+    assert (whole.info.occupied_bricks, whole.info.solid_voxels) == (parts.info.occupied_bricks, parts.info.solid_voxels)
+    o, d = mixed_rays(dims, 50000, seed=5)
+    r1, r2 = vx.VoxelRaytracer3D(whole, 50000), vx.VoxelRaytracer3D(parts, 50000)
+    assert_same_hits(r1.raytrace(o, d), r2.raytrace(o, d))
+    with pytest.raises(vx.VxError):   # a pool that does not belong to these top-level bits is refused
+        vx.World.from_parts(*dims, factor, top.data_ptr(), bounds.data_ptr(), pool.data_ptr(), occupied + 1, 0)
+    r1.close(); r2.close(); whole.close(); parts.close()

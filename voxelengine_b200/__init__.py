@@ -34,6 +34,11 @@ class WorldInfo(C.Structure):
                 ("build_ms", C.c_float), ("tiles_ms", C.c_float)]
 
 
+class SlabInfo(C.Structure):
+    _fields_ = [("brick_begin", C.c_uint64), ("brick_count", C.c_uint64), ("occupied_bricks", C.c_uint64), ("solid_voxels", C.c_uint64),
+                ("words_per_brick", C.c_uint32), ("build_ms", C.c_float)]
+
+
 class Hits(C.Structure):
     _fields_ = [("hit", C.c_void_p), ("pos", C.c_void_p), ("normal", C.c_void_p), ("steps", C.c_void_p),
                 ("voxel", C.c_void_p), ("brick", C.c_void_p), ("coarse_steps", C.c_void_p),
@@ -70,6 +75,7 @@ ABI_SYMBOLS = [
     "vx_shared_alloc", "vx_shared_open", "vx_shared_close", "vx_shared_free", "vx_device_to_host", "vx_device_fill",
     "vx_host_register", "vx_host_unregister", "vx_bands_to_host",
     "vx_world_edit", "vx_world_save", "vx_world_load",
+    "vx_slab_build_noise", "vx_slab_get_info", "vx_slab_export", "vx_slab_destroy", "vx_world_from_parts",
 ]
 
 _lib = None
@@ -119,6 +125,11 @@ def lib():
     L.vx_world_edit.argtypes = [vp, vp, sz, i32]
     L.vx_world_save.argtypes = [vp, C.c_char_p]
     L.vx_world_load.argtypes = [C.POINTER(vp), C.c_char_p, i32]
+    L.vx_slab_build_noise.argtypes = [C.POINTER(vp), u32, u32, u32, i32, u32, u32, u32, u32, u32, i32]
+    L.vx_slab_get_info.argtypes = [vp, C.POINTER(SlabInfo)]
+    L.vx_slab_export.argtypes = [vp, vp, vp, vp, vp]
+    L.vx_slab_destroy.argtypes = [vp]
+    L.vx_world_from_parts.argtypes = [C.POINTER(vp), u32, u32, u32, i32, vp, vp, vp, C.c_uint64, C.c_uint64, i32]
     L.vx_host_register.argtypes = [vp, sz]
     L.vx_host_unregister.argtypes = [vp]
     L.vx_bands_to_host.argtypes = [vp, vp, u32, u32, u32, u32, i32, vp]
@@ -259,6 +270,15 @@ class World:
         return cls(h)
 
     @classmethod
+    def from_parts(cls, X, Y, Z, factor, d_top_words, d_bounds, d_pool_words, occupied_bricks, solid_voxels, device=0):
+        """vx_world_from_parts: the world whose top-level bits, packed bounds and compact mask pool (device pointers, whole
+        world, brick order) were built slab by slab (Slab) and brought together by the caller."""
+        h = C.c_void_p()
+        _check(lib().vx_world_from_parts(C.byref(h), X, Y, Z, factor, int(d_top_words), int(d_bounds), int(d_pool_words) or None,
+                                         int(occupied_bricks), int(solid_voxels), device))
+        return cls(h)
+
+    @classmethod
     def load(cls, path, device=0):
         """A world written by save()."""
         h = C.c_void_p()
@@ -319,6 +339,34 @@ class World:
         b6 = np.zeros((n, 6), np.float32)
         _check(lib().vx_world_download_bricks(self.h, c.ctypes.data, n, occ.ctypes.data, bw.ctypes.data, b6.ctypes.data))
         return occ, bw, b6
+
+
+class Slab:
+    """One builder's z-slab of a partitioned world build (vx_slab_build_noise)."""
+
+    def __init__(self, X, Y, Z, factor, slab_index, slab_count, origin=(0, 0, 0), device=0):
+        self.h = C.c_void_p()
+        _check(lib().vx_slab_build_noise(C.byref(self.h), X, Y, Z, factor, origin[0], origin[1], origin[2], slab_index, slab_count, device))
+
+    @property
+    def info(self):
+        i = SlabInfo()
+        _check(lib().vx_slab_get_info(self.h, C.byref(i)))
+        return i
+
+    def export(self, d_top_words, d_bounds, d_pool_words, stream=0):
+        _check(lib().vx_slab_export(self.h, int(d_top_words), int(d_bounds), int(d_pool_words) or None, int(stream) or None))
+
+    def close(self):
+        if self.h:
+            lib().vx_slab_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class VoxelRaytracer3D:

@@ -35,11 +35,12 @@ __device__ __forceinline__ void brick_coords(uint32_t brick, const BuildGeom& g,
 // One warp per 8^3 tile.  Lane l owns the 16 voxels {i*32 + l}; a flattened (voxel, octave) loop
 // keeps the warp converged while lanes sit in different octaves (early-out, vx_noise.cuh).
 template <bool EARLY_OUT>
-__global__ void __launch_bounds__(256) noise_tiles(uint32_t* __restrict__ tmp, BuildGeom g, uint64_t ntiles) {
+__global__ void __launch_bounds__(256) noise_tiles(uint32_t* __restrict__ tmp, BuildGeom g, uint64_t ntiles, uint64_t tile0) {
+    // tiles tile0 .. tile0 + ntiles - 1 of the world (a z-slab of a partitioned build; the whole world with tile0 = 0) into tmp[0..]
     const uint32_t lane = threadIdx.x & 31u;
     const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
     for (uint64_t t = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < ntiles; t += warps) {
-        const uint32_t brick = (uint32_t)(t / g.tpb), sub = (uint32_t)(t % g.tpb);
+        const uint32_t brick = (uint32_t)((t + tile0) / g.tpb), sub = (uint32_t)((t + tile0) % g.tpb);
         uint32_t bx, by, bz;
         brick_coords(brick, g, bx, by, bz);
         const uint32_t f = g.f8 * 8u;
@@ -205,6 +206,16 @@ __global__ void __launch_bounds__(kScanBlock) scan_assign_slots(const uint32_t* 
     }
 }
 
+// records from packed bounds alone (world assembled from the parts of a partitioned build); slots follow from the scan
+__global__ void __launch_bounds__(256) records_from_bounds(const uint32_t* __restrict__ bounds, uint2* __restrict__ records, uint32_t nbricks) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nbricks) records[i] = make_uint2(bounds[i], 0xFFFFFFFFu);
+}
+__global__ void __launch_bounds__(256) bounds_from_records(const uint2* __restrict__ records, uint32_t* __restrict__ bounds, uint32_t nbricks) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nbricks) bounds[i] = records[i].x;
+}
+
 // ---- D: compaction ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) compact_bricks(const uint32_t* __restrict__ tmp, const uint2* __restrict__ records,
                                                       uint32_t* __restrict__ pool, uint32_t words, uint64_t total_words) {
@@ -326,8 +337,8 @@ static int check_dims(uint32_t X, uint32_t Y, uint32_t Z, int factor) {
     return VX_OK;
 }
 
-// Runs stages B-D on `d_tmp` (all tiles, brick-major) and fills `w`.
-static int finish_build(vx_world* w, const uint32_t* d_tmp, const BuildGeom& g) {
+// Stages B-D on `d_tmp` (w->nbricks bricks, brick-major): top-level bits, records (bounds + pool slot), compact pool, counters.
+static int build_bricks(vx_world* w, const uint32_t* d_tmp, const BuildGeom& g) {
     const uint32_t nb = (uint32_t)w->nbricks;
     const uint32_t words = w->words_per_brick;
     const uint32_t nwords_top = (nb + 31) / 32;
@@ -357,6 +368,13 @@ static int finish_build(vx_world* w, const uint32_t* d_tmp, const BuildGeom& g) 
     const uint64_t total_words = (uint64_t)nb * words;
     compact_bricks<<<(uint32_t)((total_words / 4 + 255) / 256), 256>>>(d_tmp, w->d_records, w->d_pool, words, total_words);
     VX_CUDA(cudaGetLastError());
+    cudaFree(d_counters);
+    cudaFree(d_block_sums);
+    return VX_OK;
+}
+
+// Stage E: the traversal copies (padded linear grid) from top bits + records; the tiled-order records are freed.
+static int build_traversal(vx_world* w, const BuildGeom& g) {
     const uint64_t pcells = (uint64_t)(w->cx + 2) * (w->cy + 2) * (w->cz + 2);
     VX_REQUIRE(pcells < (1ull << 31), "padded coarse grid exceeds a 31-bit cell index");
     VX_CUDA(cudaMalloc(&w->d_ptop, (size_t)((pcells + 31) / 32) * 4));
@@ -365,9 +383,13 @@ static int finish_build(vx_world* w, const uint32_t* d_tmp, const BuildGeom& g) 
     VX_CUDA(cudaGetLastError());
     VX_CUDA(cudaDeviceSynchronize());
     cudaFree(w->d_records); w->d_records = nullptr;
-    cudaFree(d_counters);
-    cudaFree(d_block_sums);
     return VX_OK;
+}
+
+static int finish_build(vx_world* w, const uint32_t* d_tmp, const BuildGeom& g) {
+    int rc = build_bricks(w, d_tmp, g);
+    if (rc) return rc;
+    return build_traversal(w, g);
 }
 
 static void free_world(vx_world* w) {
@@ -415,8 +437,8 @@ static int build_common(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int 
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         const uint64_t want = (ntiles + 7) / 8; // 8 warps per block
         const uint32_t blocks = (uint32_t)(want < (uint64_t)sms * 64 ? want : (uint64_t)sms * 64);
-        if (flags & 1u) noise_tiles<false><<<blocks, 256>>>(d_tmp, g, ntiles);
-        else noise_tiles<true><<<blocks, 256>>>(d_tmp, g, ntiles);
+        if (flags & 1u) noise_tiles<false><<<blocks, 256>>>(d_tmp, g, ntiles, 0);
+        else noise_tiles<true><<<blocks, 256>>>(d_tmp, g, ntiles, 0);
     }
     VX_TRY(cudaGetLastError());
     VX_TRY(cudaEventRecord(em));
@@ -523,5 +545,157 @@ extern "C" int vx_world_download_bricks(const vx_world* w, const uint32_t* coars
     if (bounds6) VX_TRY(cudaMemcpy(bounds6, d_b6, n * 24, cudaMemcpyDeviceToHost));
 #undef VX_TRY
     cleanup();
+    return VX_OK;
+}
+
+// ---- partitioned build (BASELINE configs[4]) ------------------------------------------------------------------
+// The coarse grid's 8-cell z-tiles are dealt to `slab_count` builders in contiguous runs; in the reference's tiled coarse
+// index a run of z-tiles is a contiguous range of bricks, and pool slots follow brick order, so the slabs' top-level bits,
+// bounds and compact pools simply concatenate into what the single-device build produces, word for word.  Each builder runs
+// the voxel kernel and stages B-D on its slab (vx_slab_build_noise), the parts travel between the devices (the caller's job:
+// torch.distributed / NCCL all-gather of three flat arrays), and vx_world_from_parts re-derives the slots by the same scan
+// and builds the traversal copies.
+struct vx_slab {
+    vx_world* part = nullptr; // nbricks = the slab's bricks; d_top, d_records, d_pool valid; no traversal copies
+    uint64_t brick_begin = 0;
+    float build_ms = 0.0f;
+};
+
+static void slab_range(uint32_t cx, uint32_t cy, uint32_t cz, uint32_t index, uint32_t count, uint64_t& begin, uint64_t& n) {
+    const uint64_t zt = cz / 8u, per_zt = (uint64_t)(cx / 8u) * (cy / 8u) * 512u;
+    const uint64_t z0 = zt * index / count, z1 = zt * (index + 1u) / count;
+    begin = z0 * per_zt; n = (z1 - z0) * per_zt;
+}
+
+extern "C" int vx_slab_build_noise(vx_slab** out, uint32_t X, uint32_t Y, uint32_t Z, int factor, uint32_t x0, uint32_t y0, uint32_t z0,
+                                   uint32_t slab_index, uint32_t slab_count, int device) {
+    VX_REQUIRE(out != nullptr, "out is NULL");
+    *out = nullptr;
+    int rc = check_dims(X, Y, Z, factor);
+    if (rc) return rc;
+    VX_REQUIRE(slab_count >= 1 && slab_index < slab_count, "slab_index must be below slab_count");
+    VX_REQUIRE((uint64_t)x0 + X < (1ull << 31) && (uint64_t)y0 + Y < (1ull << 31) && (uint64_t)z0 + Z < (1ull << 31), "window exceeds int range");
+    DeviceGuard guard(device);
+    if (!guard.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+    vx_world* w = new vx_world();
+    w->device = device; w->X = X; w->Y = Y; w->Z = Z; w->factor = factor;
+    w->cx = X / factor; w->cy = Y / factor; w->cz = Z / factor;
+    w->words_per_brick = (uint32_t)factor * factor * factor / 32;
+    uint64_t begin = 0, n = 0;
+    slab_range(w->cx, w->cy, w->cz, slab_index, slab_count, begin, n);
+    w->nbricks = n;
+    vx_slab* s = new vx_slab();
+    s->part = w; s->brick_begin = begin;
+    if (n == 0) { *out = s; return VX_OK; } // more builders than z-tiles: an empty slab
+    BuildGeom g;
+    g.cx = w->cx; g.cy = w->cy; g.cz = w->cz; g.f8 = factor / 8; g.tpb = g.f8 * g.f8 * g.f8;
+    g.x0 = x0; g.y0 = y0; g.z0 = z0; g.X = X; g.Y = Y;
+    const uint64_t ntiles = n * g.tpb;
+    uint32_t* d_tmp = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    auto fail = [&](int code) { cudaFree(d_tmp); if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); free_world(w); delete s; return code; };
+#define VX_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(cuda_fail(e_, #call, __FILE__, __LINE__)); } while (0)
+    VX_TRY(cudaMalloc(&d_tmp, (size_t)ntiles * 64));
+    VX_TRY(cudaEventCreate(&e0));
+    VX_TRY(cudaEventCreate(&e1));
+    VX_TRY(cudaEventRecord(e0));
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    const uint64_t want = (ntiles + 7) / 8;
+    const uint32_t blocks = (uint32_t)(want < (uint64_t)sms * 64 ? want : (uint64_t)sms * 64);
+    noise_tiles<true><<<blocks, 256>>>(d_tmp, g, ntiles, begin * g.tpb);
+    VX_TRY(cudaGetLastError());
+    rc = build_bricks(w, d_tmp, g);
+    if (rc) return fail(rc);
+    VX_TRY(cudaEventRecord(e1));
+    VX_TRY(cudaEventSynchronize(e1));
+    VX_TRY(cudaEventElapsedTime(&s->build_ms, e0, e1));
+#undef VX_TRY
+    cudaFree(d_tmp); cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *out = s;
+    return VX_OK;
+}
+
+extern "C" int vx_slab_get_info(const vx_slab* s, vx_slab_info* info) {
+    VX_REQUIRE(s && info, "NULL argument");
+    info->brick_begin = s->brick_begin; info->brick_count = s->part->nbricks;
+    info->occupied_bricks = s->part->occupied; info->solid_voxels = s->part->solid_voxels;
+    info->words_per_brick = s->part->words_per_brick; info->build_ms = s->build_ms;
+    return VX_OK;
+}
+
+extern "C" int vx_slab_export(const vx_slab* s, uint32_t* d_top_words, uint32_t* d_bounds, uint32_t* d_pool_words, void* stream) {
+    VX_REQUIRE(s != nullptr, "slab is NULL");
+    const vx_world* w = s->part;
+    if (w->nbricks == 0) return VX_OK;
+    VX_REQUIRE(d_top_words && d_bounds && (d_pool_words || w->occupied == 0), "NULL argument");
+    DeviceGuard guard(w->device);
+    cudaStream_t cs = (cudaStream_t)stream;
+    const uint32_t nb = (uint32_t)w->nbricks;
+    VX_CUDA(cudaMemcpyAsync(d_top_words, w->d_top, (size_t)(nb / 32) * 4, cudaMemcpyDeviceToDevice, cs));
+    bounds_from_records<<<(nb + 255) / 256, 256, 0, cs>>>(w->d_records, d_bounds, nb);
+    VX_CUDA(cudaGetLastError());
+    if (w->occupied) VX_CUDA(cudaMemcpyAsync(d_pool_words, w->d_pool, (size_t)w->occupied * w->words_per_brick * 4, cudaMemcpyDeviceToDevice, cs));
+    return VX_OK;
+}
+
+extern "C" int vx_slab_destroy(vx_slab* s) {
+    if (!s) return VX_OK;
+    DeviceGuard guard(s->part->device);
+    free_world(s->part);
+    delete s;
+    return VX_OK;
+}
+
+extern "C" int vx_world_from_parts(vx_world** out, uint32_t X, uint32_t Y, uint32_t Z, int factor, const uint32_t* d_top_words,
+                                   const uint32_t* d_bounds, const uint32_t* d_pool_words, uint64_t occupied_bricks, uint64_t solid_voxels, int device) {
+    VX_REQUIRE(out && d_top_words && d_bounds && (d_pool_words || occupied_bricks == 0), "NULL argument");
+    *out = nullptr;
+    int rc = check_dims(X, Y, Z, factor);
+    if (rc) return rc;
+    DeviceGuard guard(device);
+    if (!guard.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+    vx_world* w = new vx_world();
+    w->device = device; w->X = X; w->Y = Y; w->Z = Z; w->factor = factor;
+    w->cx = X / factor; w->cy = Y / factor; w->cz = Z / factor;
+    w->nbricks = (uint64_t)w->cx * w->cy * w->cz;
+    w->words_per_brick = (uint32_t)factor * factor * factor / 32;
+    w->occupied = occupied_bricks; w->solid_voxels = solid_voxels;
+    BuildGeom g{};
+    g.cx = w->cx; g.cy = w->cy; g.cz = w->cz; g.f8 = factor / 8; g.tpb = g.f8 * g.f8 * g.f8; g.X = X; g.Y = Y;
+    const uint32_t nb = (uint32_t)w->nbricks, nwords_top = nb / 32;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    uint32_t* d_block_sums = nullptr; unsigned long long* d_total = nullptr;
+    auto fail = [&](int code) { cudaFree(d_block_sums); cudaFree(d_total); if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); free_world(w); return code; };
+#define VX_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(cuda_fail(e_, #call, __FILE__, __LINE__)); } while (0)
+    VX_TRY(cudaEventCreate(&e0)); VX_TRY(cudaEventCreate(&e1));
+    VX_TRY(cudaEventRecord(e0));
+    VX_TRY(cudaMalloc(&w->d_top, (size_t)nwords_top * 4));
+    VX_TRY(cudaMemcpy(w->d_top, d_top_words, (size_t)nwords_top * 4, cudaMemcpyDeviceToDevice));
+    VX_TRY(cudaMalloc(&w->d_records, (size_t)nb * sizeof(uint2)));
+    records_from_bounds<<<(nb + 255) / 256, 256>>>(d_bounds, w->d_records, nb);
+    const uint32_t nblocks = (nwords_top + kScanBlock - 1) / kScanBlock;
+    VX_TRY(cudaMalloc(&d_block_sums, (size_t)nblocks * 4));
+    VX_TRY(cudaMalloc(&d_total, 8));
+    scan_block_sums<<<nblocks, kScanBlock>>>(w->d_top, nwords_top, d_block_sums);
+    scan_block_offsets<<<1, 1024>>>(d_block_sums, nblocks, d_total);
+    scan_assign_slots<<<nblocks, kScanBlock>>>(w->d_top, nwords_top, d_block_sums, w->d_records);
+    VX_TRY(cudaGetLastError());
+    unsigned long long total = 0;
+    VX_TRY(cudaMemcpy(&total, d_total, 8, cudaMemcpyDeviceToHost));
+    if (total != occupied_bricks) { set_error("vx_world_from_parts: the top-level bits name a different number of bricks than the pool holds"); return fail(VX_ERR_INVALID); }
+    const size_t pool_words = (size_t)(w->occupied ? w->occupied : 1) * w->words_per_brick;
+    VX_TRY(cudaMalloc(&w->d_pool, pool_words * 4));
+    w->pool_capacity = w->occupied ? w->occupied : 1; w->pool_used = w->occupied;
+    if (w->occupied) VX_TRY(cudaMemcpy(w->d_pool, d_pool_words, pool_words * 4, cudaMemcpyDeviceToDevice));
+    else VX_TRY(cudaMemset(w->d_pool, 0, pool_words * 4));
+    rc = build_traversal(w, g);
+    if (rc) return fail(rc);
+    VX_TRY(cudaEventRecord(e1));
+    VX_TRY(cudaEventSynchronize(e1));
+    VX_TRY(cudaEventElapsedTime(&w->build_ms, e0, e1));
+#undef VX_TRY
+    cudaFree(d_block_sums); cudaFree(d_total); cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *out = w;
     return VX_OK;
 }

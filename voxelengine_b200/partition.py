@@ -319,3 +319,53 @@ class HostFrame:
         except BufferError:   # a caller still holds a view of `array`; the mapping goes with the last reference
             pass
         self._map = None
+
+
+def build_world_partitioned(X, Y, Z, factor=8, device=0, origin=(0, 0, 0), group=None, rank=None, world_size=None):
+    """The noise world built by all ranks together (BASELINE configs[4]): rank r runs the voxel kernel on its z-slab
+    (vx_slab_build_noise), the slabs' top-level bits, packed bounds and compact mask pools are all-gathered (plain bulk
+    collectives: NCCL over NVLink on GPUs), and every rank assembles the same world from the parts (vx_world_from_parts) —
+    word for word the world vx_world_build_noise builds on one device.  Collective.  Returns (World, timings dict in ms:
+    slab = this rank's voxel kernel + brick analysis, exchange = the collectives, assemble = vx_world_from_parts)."""
+    import time
+    import voxelengine_b200 as vx
+    rank = dist.get_rank(group) if rank is None else rank
+    world_size = dist.get_world_size(group) if world_size is None else world_size
+    dev = torch.device("cuda", device)
+    slab = vx.Slab(X, Y, Z, factor, rank, world_size, origin=origin, device=device)
+    info = slab.info
+    wpb = int(info.words_per_brick)
+    nb = (X // factor) * (Y // factor) * (Z // factor)
+    mine = torch.tensor([int(info.brick_begin), int(info.brick_count), int(info.occupied_bricks), int(info.solid_voxels)], dtype=torch.int64, device=dev)
+    parts = [torch.zeros_like(mine) for _ in range(world_size)]
+    torch.cuda.synchronize(device)
+    t0 = time.perf_counter()
+    if world_size > 1:
+        dist.all_gather(parts, mine, group=group)
+    else:
+        parts = [mine]
+    parts = [[int(v) for v in p.cpu()] for p in parts]
+    occupied = sum(p[2] for p in parts)
+    solid = sum(p[3] for p in parts)
+    top = torch.empty(nb // 32, dtype=torch.int32, device=dev)
+    bounds = torch.empty(nb, dtype=torch.int32, device=dev)
+    pool = torch.empty(max(occupied, 1) * wpb, dtype=torch.int32, device=dev)
+    slot0 = [sum(p[2] for p in parts[:r]) for r in range(world_size)]
+    views = [(top[p[0] // 32:(p[0] + p[1]) // 32], bounds[p[0]:p[0] + p[1]], pool[slot0[r] * wpb:(slot0[r] + p[2]) * wpb])
+             for r, p in enumerate(parts)]
+    slab.export(views[rank][0].data_ptr(), views[rank][1].data_ptr(), views[rank][2].data_ptr() if parts[rank][2] else 0,
+                stream=torch.cuda.current_stream(device).cuda_stream)
+    if world_size > 1:
+        # every part goes from its builder to everybody: one broadcast per part and builder, straight into place
+        for r in range(world_size):
+            for v in views[r]:
+                if v.numel():
+                    dist.broadcast(v, src=dist.get_global_rank(group, r) if group is not None else r, group=group)
+    torch.cuda.synchronize(device)
+    t1 = time.perf_counter()
+    slab.close()
+    world = vx.World.from_parts(X, Y, Z, factor, top.data_ptr(), bounds.data_ptr(), pool.data_ptr(), occupied, solid, device=device)
+    torch.cuda.synchronize(device)
+    t2 = time.perf_counter()
+    return world, {"slab": float(info.build_ms), "exchange": (t1 - t0) * 1e3, "assemble": (t2 - t1) * 1e3,
+                   "slab_bricks": int(info.brick_count), "slab_occupied": int(info.occupied_bricks)}
