@@ -23,6 +23,7 @@ struct WorldView {
     const uint32_t* __restrict__ pool;  // occupied bricks only, words_per_brick words each, in-brick tiled index
     int cx, cy, cz;                     // coarse dims
     int factor;
+    float inv_factor;                   // 1 / factor when factor is a power of two (then x * inv_factor == x / factor exactly), else 0
     uint32_t words_per_brick;           // factor^3 / 32
     uint32_t tiles_x, tiles_xy;         // cx/8, (cx/8)*(cy/8)
     // traversal copies in our own layout: x-fastest linear grid with a one-cell border on every side

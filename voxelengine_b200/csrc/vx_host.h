@@ -66,6 +66,7 @@ struct vx_world {
         vx::WorldView v;
         v.top = d_top; v.records = d_records; v.pool = d_pool;
         v.cx = (int)cx; v.cy = (int)cy; v.cz = (int)cz; v.factor = factor;
+        v.inv_factor = (factor & (factor - 1)) == 0 ? 1.0f / (float)factor : 0.0f;
         v.words_per_brick = words_per_brick; v.tiles_x = cx / 8; v.tiles_xy = (cx / 8) * (cy / 8);
         v.ptop = d_ptop; v.precords = d_precords; v.pnx = (int)cx + 2; v.pnxy = ((int)cx + 2) * ((int)cy + 2);
         magic_for((uint32_t)v.pnx, v.magic_x, v.shift_x);
@@ -104,6 +105,7 @@ struct vx_tracer {
     int fused_shade = 0;  // vx_tracer_set_fused_shade
     bool primary_only = false; unsigned long long* last_queue_count = nullptr; // vx_bounce_rays reuses vx_render's primary pass
     cudaStream_t l2_stream = nullptr; const void* l2_base = nullptr; bool l2_tried = false; // pin_top_level (vx_trace.cu)
+    uint32_t* d_tile_trace = nullptr; size_t tile_trace_words = 0, tile_trace_tiles = 0; // VX_TILE_TRACE diagnostics (vx_trace.cu)
     vx::BatchPipe* batch = nullptr; // vx_trace: pinned staging ring, copy threads and streams of the host-array batch call
     bool timing = false; int timed_kernels = 0; cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // vx_tracer_set_timing
 };

@@ -81,11 +81,9 @@ __device__ __forceinline__ int steps_from_start(const Lane& L, int x, int y, int
 // p / factor (start = origin / factor, VolumeRaytracer.cu:361, and the re-seeding of :438).  For a power-of-two factor
 // x * (1 / factor) is the same float as x / factor — both are the correctly rounded value of the same real number.
 __device__ __forceinline__ V3 to_brick_units(const WorldView& w, V3 p) {
+    const float inv_f = w.inv_factor;
+    if (inv_f != 0.0f) return mk(fmul(p.x, inv_f), fmul(p.y, inv_f), fmul(p.z, inv_f));
     const float ff = (float)w.factor;
-    if ((w.factor & (w.factor - 1)) == 0) {
-        const float inv_f = fdiv(1.0f, ff);
-        return mk(fmul(p.x, inv_f), fmul(p.y, inv_f), fmul(p.z, inv_f));
-    }
     return mk(fdiv(p.x, ff), fdiv(p.y, ff), fdiv(p.z, ff));
 }
 
@@ -553,8 +551,8 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
     const float l0 = (float)(b & 31u), l1 = (float)((b >> 5) & 31u), l2 = (float)((b >> 10) & 31u);
     const float h0 = (float)(((b >> 15) & 31u) + 1u), h1 = (float)(((b >> 20) & 31u) + 1u), h2 = (float)(((b >> 25) & 31u) + 1u);
     V3 lo, hi;
-    if ((w.factor & (w.factor - 1)) == 0) { // x / 2^k == x * 2^-k exactly
-        const float inv_f = fdiv(1.0f, (float)w.factor);
+    if (w.inv_factor != 0.0f) { // x / 2^k == x * 2^-k exactly
+        const float inv_f = w.inv_factor;
         lo = mk(fadd(fmul(l0, inv_f), (float)qx), fadd(fmul(l1, inv_f), (float)qy), fadd(fmul(l2, inv_f), (float)qz));
         hi = mk(fadd(fmul(h0, inv_f), (float)qx), fadd(fmul(h1, inv_f), (float)qy), fadd(fmul(h2, inv_f), (float)qz));
     } else {

@@ -110,6 +110,8 @@ struct FrameParams {
     uint32_t band_count, band_index; // multi-GPU: 8-row bands dealt round-robin, this launch renders bands == index (mod count)
     uint32_t mcols;            // 16x8 macro tiles per band
     unsigned long long ids;    // ray ids of this launch = mcols * my_bands * 128
+    uint32_t* __restrict__ tile_trace; // diagnostics (VX_TILE_TRACE=1), else NULL: per 8x4 tile of the launch, the SM cycles it kept its
+                                       // warp and (second half of the array) the low word of %globaltimer when the warp drew it
 };
 
 __device__ __forceinline__ void put_pixel(uint8_t* __restrict__ bgra, uint32_t W, uint32_t H, int x, int y, V3 c) {
@@ -234,6 +236,7 @@ struct PrimaryPolicy {
     ShadowQueue q;
     uint32_t pix; // per lane: x | y << 15 | crosshair thread << 30 | hit staged << 31
     float4* stage_rec; uint32_t* stage_aux; // shared memory, one slot per thread (x4 words with STATS)
+    uint32_t* tile_slot;                    // shared memory, two words per warp (tile trace): the tile this warp runs, the clock at its draw
 
     __device__ __forceinline__ PrimaryPolicy(const FrameParams& fp, uint8_t* b, int32_t* sp, unsigned long long* st, ShadowQueue sq)
         : f(fp), bgra(b), steps_plane(sp), stats(st), q(sq), pix(0) {}
@@ -244,10 +247,14 @@ struct PrimaryPolicy {
     // the sun rays that shadow_rays later draws 32 at a time are then neighbours on the screen (coherent), which they are
     // not if every lane appends the moment it finishes.
     __device__ __forceinline__ void flush() {
+        const uint32_t lane = threadIdx.x & 31u;
+        if (f.tile_trace && lane == 0u && tile_slot[0] != 0xFFFFFFFFu) {
+            f.tile_trace[tile_slot[0]] = (uint32_t)clock64() - tile_slot[1];
+            tile_slot[0] = 0xFFFFFFFFu;
+        }
         const bool staged = pix >> 31;
         const uint32_t m = __ballot_sync(kFull, staged);
         if (!m) return;
-        const uint32_t lane = threadIdx.x & 31u;
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(q.count, (unsigned long long)__popc(m));
         base = __shfl_sync(kFull, base, 0);
@@ -274,6 +281,11 @@ struct PrimaryPolicy {
 
     __device__ __forceinline__ void init(const WorldView& w, unsigned long long id64, Lane& L) {
         const uint32_t id = (uint32_t)id64;
+        if (f.tile_trace && (id & 31u) == 0u) {
+            unsigned long long ns;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+            tile_slot[0] = id >> 5; tile_slot[1] = (uint32_t)clock64(); f.tile_trace[(f.ids >> 5) + (id >> 5)] = (uint32_t)ns;
+        }
         const uint32_t j = id & 31u, k = (id >> 5) & 3u, macro = id >> 7;
         const uint32_t lband = macro / f.mcols, mcol = macro - lband * f.mcols;
 #if VX_TILE_SHAPE == 0   // four 8x4 tiles per 16x8 macro tile
@@ -514,8 +526,11 @@ __global__ void __launch_bounds__(128, VX_MIN_BLOCKS) primary_rays(WorldView w, 
                                                                    unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
     __shared__ float4 stage_rec[128];
     __shared__ uint32_t stage_aux[STATS ? 512 : 128];
+    __shared__ uint32_t tile_slots[8];
+    if (threadIdx.x < 8) tile_slots[threadIdx.x] = 0xFFFFFFFFu;
+    __syncthreads();
     PrimaryPolicy<NORM, STATS, ORTHO> pol(f, bgra, steps_plane, stats, q);
-    pol.stage_rec = stage_rec; pol.stage_aux = stage_aux;
+    pol.stage_rec = stage_rec; pol.stage_aux = stage_aux; pol.tile_slot = tile_slots + 2 * (threadIdx.x >> 5);
     run_lanes<false, STATS>(w, pol, next);
 }
 template <int NORM, bool STATS, bool FUSE>
@@ -573,6 +588,7 @@ extern "C" int vx_tracer_destroy(vx_tracer* t) {
     if (t->copy_stream) cudaStreamDestroy(t->copy_stream);
     if (t->stream) cudaStreamDestroy(t->stream);
     destroy_batch_pipe(t->batch);
+    cudaFree(t->d_tile_trace);
     delete t;
     return VX_OK;
 }
@@ -584,6 +600,8 @@ static int persistent_blocks(vx_tracer* t, K kernel, unsigned long long ids, uns
     int per_sm = 0;
     VX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 128, 0));
     if (per_sm < 1) per_sm = 1;
+    static const int cap = [] { const char* e = getenv("VX_BLOCKS_PER_SM"); return e ? atoi(e) : 0; }(); // experiments: fewer resident blocks
+    if (cap > 0 && cap < per_sm) per_sm = cap;
     const unsigned long long full = (unsigned long long)per_sm * (unsigned long long)(t->sm_count > 0 ? t->sm_count : 148);
     const unsigned long long need = (ids + 127) / 128;
     blocks = (unsigned)(need < full ? need : full);
@@ -968,6 +986,19 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     unsigned long long* st = (unsigned long long*)opts->d_stats;
     cudaStream_t cs = (cudaStream_t)stream;
     pin_top_level(t, cs);
+    f.tile_trace = nullptr;
+    static const bool trace = [] { const char* e = getenv("VX_TILE_TRACE"); return e && atoi(e) != 0; }();
+    if (trace) { // diagnostics: a timeline of the launch's tiles (tools/tile_trace.py)
+        const size_t words = (size_t)(f.ids >> 5) * 2;
+        if (t->tile_trace_words < words) {
+            VX_CUDA(cudaStreamSynchronize(cs));
+            cudaFree(t->d_tile_trace); t->d_tile_trace = nullptr; t->tile_trace_words = 0;
+            VX_CUDA(cudaMalloc(&t->d_tile_trace, words * 4));
+            t->tile_trace_words = words;
+        }
+        t->tile_trace_tiles = (size_t)(f.ids >> 5);
+        f.tile_trace = t->d_tile_trace;
+    }
     const bool shadow_pass = opts->shadows && !opts->debug_view;
     ShadowQueue q{nullptr, nullptr, nullptr, nullptr};
     if (shadow_pass) { // per-frame queue of primary hits waiting for their sun ray (one entry per pixel of this launch at most)
@@ -1203,3 +1234,18 @@ extern "C" int vx_debug_fine_stats(unsigned long long out[8], int device) {
     return VX_OK;
 }
 #endif
+
+// diagnostics (VX_TILE_TRACE=1): for every 8x4 tile of the last vx_render, the SM cycles it kept its warp and the low word of
+// %globaltimer (ns) at which the warp drew it; out arrays hold `capacity` entries, *n = tiles of that launch
+extern "C" int vx_debug_tile_trace(vx_tracer* t, uint32_t* out_cycles, uint32_t* out_start_ns, size_t capacity, size_t* n) {
+    VX_REQUIRE(t && n, "NULL argument");
+    *n = 0;
+    if (!t->d_tile_trace) return VX_OK;
+    DeviceGuard guard(t->device);
+    VX_CUDA(cudaDeviceSynchronize());
+    const size_t m = t->tile_trace_tiles < capacity ? t->tile_trace_tiles : capacity;
+    if (out_cycles) VX_CUDA(cudaMemcpy(out_cycles, t->d_tile_trace, m * 4, cudaMemcpyDeviceToHost));
+    if (out_start_ns) VX_CUDA(cudaMemcpy(out_start_ns, t->d_tile_trace + t->tile_trace_tiles, m * 4, cudaMemcpyDeviceToHost));
+    *n = m;
+    return VX_OK;
+}
