@@ -307,6 +307,19 @@ class HostFrame:
         if self.part.world_size > 1:
             dist.barrier(group=self.group)
 
+    def mark(self, stream=None):
+        """An event after the copies enqueued so far (on the copy stream of render_and_store, or on `stream` for store()):
+        wait(mark()) is fence() for exactly this frame, so a consumer that keeps two host frames can let the ranks start frame
+        k + 1 before it waits for frame k — the inter-process barrier then overlaps rendering instead of adding to it."""
+        ev = torch.cuda.Event()
+        ev.record(self._copy_stream if (stream is None and self._copy_stream is not None) else stream)
+        return ev
+
+    def wait(self, event):
+        event.synchronize()
+        if self.part.world_size > 1:
+            dist.barrier(group=self.group)
+
     def close(self):
         if self._map is None:
             return
