@@ -7,7 +7,7 @@
  * addition returns the locals the parity contract compares: coarse cell, brick index (:419),
  * fine cell, per-level step counts, and the work counters C/K/E of SURVEY.md §8(d).
  * Parity status: pinned against the reference's own VolumeRaytracer.cu compiled for the host
- * (oracle/_ref/libvxref_host.so; tests/test_oracle_vs_ref.py).
+ * (oracle/_ref/libvxref_host.so; tests/test_oracle.py, tests/test_reference_pins.py).
  */
 #include "vxo.h"
 #include "vxo_common.h"

@@ -7,7 +7,7 @@
  *   VoxelWorldBuilder.cu:4-35 (PerlinNoise, PopulateVoxels);
  *   VolumeRaytracer.cuh:379-516 (GenerateLowresVoxelBuffer).
  * Parity status: pinned for the brickmap build against the reference's own
- * GenerateLowresVoxelBuffer compiled for the host (oracle/_ref, tests/test_oracle_vs_ref.py);
+ * GenerateLowresVoxelBuffer compiled for the host (oracle/_ref, tests/test_oracle.py, tests/test_reference_pins.py);
  * the noise chain is pinned against the reference's cuda_noise.cuh compiled as plain C++
  * (x86 float->uint mode) and, on the GPU box, against the reference's PopulateVoxels kernel.
  */

@@ -6,6 +6,7 @@
 // ("policies") that feed it, the launches and the C ABI.
 #include "vx_host.h"
 #include "vx_march.cuh"
+#include "vx_noise.cuh"
 #include <stdlib.h>
 #include <string.h>
 #include <condition_variable>
@@ -483,16 +484,7 @@ __global__ void __launch_bounds__(256) shade_pixels(FrameParams f, uint8_t* __re
 
 // Incoherent secondary rays (BASELINE config 5): the ambient-occlusion sample loop of Renderer.cu:121-165, sample i = 0.
 // One thread per queued primary hit; ray order follows the queue, `pixels` says which pixel each ray belongs to.
-__device__ __forceinline__ uint32_t noise_hash(uint32_t seed) { // cuda_noise.cuh:44-54
-    seed = (seed + 0x7ed55d16u) + (seed << 12);
-    seed = (seed ^ 0xc761c23cu) ^ (seed >> 19);
-    seed = (seed + 0x165667b1u) + (seed << 5);
-    seed = (seed + 0xd3a2646cu) ^ (seed << 9);
-    seed = (seed + 0xfd7046c5u) + (seed << 3);
-    seed = (seed ^ 0xb55a4f09u) ^ (seed >> 16);
-    return seed;
-}
-__device__ __forceinline__ float random_float(uint32_t seed) { return fdiv((float)noise_hash(seed), (float)0xffffffffu); } // :66-71
+__device__ __forceinline__ float random_float(uint32_t seed) { return fdiv((float)hash32(seed), (float)0xffffffffu); } // cuda_noise.cuh:66-71 (hash: vx_noise.cuh)
 
 template <int NORM>
 __global__ void __launch_bounds__(256) bounce_setup(FrameParams f, ShadowQueue q, float* __restrict__ origins, float* __restrict__ dirs,
