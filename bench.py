@@ -38,6 +38,9 @@ DIMS_W2 = (8192, 512, 8192)
 CAMERAS = {
     "overview": dict(xz=(4096, 7936), lift=128, euler=(-0.5, 0.0, 0.0)),
     "grazing": dict(xz=(4096, 4096), lift=0, euler=(-0.05, 0.8, 0.0)),
+    # not a config of BASELINE.json: from one corner along the diagonal, traversals that can meet the step cap before the far
+    # border (tests/test_gpu_w2_scale.py checks it against the oracle, tools/sweep_kernels.py times it)
+    "diagonal": dict(xz=(8180, 8180), lift=0, euler=(-0.02, 0.7853982, 0.0)),
 }
 WORKLOADS = {
     "w2-4k": dict(dims=DIMS_W2, W=3840, H=2160, camera="overview",

@@ -17,7 +17,7 @@ flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
 opts = vx.RenderOpts(0, 0, 0, 1, 1, vx.NORM_DEVICE, 0, 0, 0, 0, None)
 stream = torch.cuda.current_stream().cuda_stream
 rt.set_timing(True)
-for name in (["overview", "grazing"] if isinstance(wl["camera"], str) else ["camera"]):
+for name in (["overview", "grazing", "diagonal"] if isinstance(wl["camera"], str) else ["camera"]):
     cam, pos = bench.camera_for(vx, rt, wl["dims"], bench.CAMERAS[name] if name in bench.CAMERAS else wl["camera"])
     acc = [0.0] * 4
     for i in range(9):
