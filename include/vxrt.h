@@ -206,6 +206,25 @@ int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_re
 int vx_render_host(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* opts,
                    void* h_bgra, uint32_t W, uint32_t H);
 
+/* vx_render without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It needs no
+ * tracer: the frame's scratch (three 8-byte counters and the queue of primary hits waiting for their sun ray, 72 bytes per ray
+ * id) is ONE file-scope device array of 256 + 72 * VX_STATIC_MAX_RAY_IDS bytes (18 MiB) that every GPU loading the library
+ * holds until exit.  Same kernels, same pixels as vx_render(t, cam, env, opts, d_bgra, d_steps, W, H, stream).
+ *   - limit: ray ids of the call = ceil(columns / 16) * (8-row bands of this call) * 128 <= VX_STATIC_MAX_RAY_IDS, i.e. frames up
+ *     to 640x360 (tile_* / band_* fields of opts count only their share: larger frames can be rendered in pieces); beyond it the
+ *     call returns VX_ERR_INVALID and vx_last_error() says how many ids were needed;
+ *   - cam->tan_half must be > 0 (vx_device_tanf once at set-up; evaluating it per call would allocate) and opts->d_stats NULL;
+ *   - the call itself runs cudaMemsetAsync (the counters) and up to four kernel launches on `stream`, nothing else: no cudaMalloc,
+ *     cudaFree or allocating library routine.  The first call on a device looks the array's address up
+ *     (cudaGetSymbolAddress) — make it once outside graph capture;
+ *   - ALL calls on a device share the array, and it keeps the last call's contents (the call clears what must start at zero):
+ *     calls that overlap on the GPU (two streams, two host threads, two captured graphs replayed at once) race; each process has its own copy.
+ *     Order them on one stream or with events. */
+#define VX_STATIC_MAX_RAY_IDS 262144ull
+int vx_render_static(const vx_world* world, const vx_camera* cam, const vx_env* env, const vx_render_opts* opts,
+                     void* d_bgra, int32_t* d_steps, uint32_t W, uint32_t H, void* stream);
+
 /* Incoherent secondary rays (BASELINE config 5).  For every primary hit of the frame (cam, opts: checkerboard, frame_number,
  * tile/band fields and norm_mode are honoured) generates the ambient-occlusion sample ray of calculateColor's sample loop
  * (Renderer.cu:121-165, sample i = 0): seed = thread_y * W + thread_x + (frame_number + 1) * 1000, direction =

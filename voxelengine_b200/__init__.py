@@ -20,6 +20,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("VXRT_LIB") or os.path.join(_HERE, "lib", "libvxrt.so")  # VXRT_LIB: tuning builds (tools/)
 
 NORM_DEVICE, NORM_HOST, NORM_NONE = 0, 1, 2
+STATIC_MAX_RAY_IDS = 262144  # VX_STATIC_MAX_RAY_IDS of include/vxrt.h (World.render_static)
 MAX_STEPS = 2048
 
 
@@ -71,7 +72,7 @@ ABI_SYMBOLS = [
     "vx_last_error", "vx_version", "vx_device_count", "vx_world_build_noise", "vx_world_build_noise_full",
     "vx_world_from_dense_bits", "vx_world_destroy", "vx_world_get_info", "vx_world_download", "vx_world_download_bricks", "vx_tracer_create",
     "vx_tracer_destroy", "vx_trace", "vx_trace_device", "vx_hits_postprocess", "vx_get_directions", "vx_render",
-    "vx_render_host", "vx_bounce_rays", "vx_tracer_set_timing", "vx_tracer_set_fused_shade", "vx_tracer_frame_times", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
+    "vx_render_host", "vx_render_static", "vx_bounce_rays", "vx_tracer_set_timing", "vx_tracer_set_fused_shade", "vx_tracer_frame_times", "vx_device_tanf", "vx_device_normalize", "vx_measure_read_bandwidth",
     "vx_shared_alloc", "vx_shared_open", "vx_shared_close", "vx_shared_free", "vx_device_to_host", "vx_device_fill",
     "vx_host_register", "vx_host_unregister", "vx_bands_to_host",
     "vx_world_edit", "vx_world_save", "vx_world_load",
@@ -108,6 +109,7 @@ def lib():
     L.vx_get_directions.argtypes = [vp, vp, vp, vp]
     L.vx_get_directions.restype = None
     L.vx_render.argtypes = [vp, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts), vp, vp, u32, u32, vp]
+    L.vx_render_static.argtypes = [vp, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts), vp, vp, u32, u32, vp]
     L.vx_render_host.argtypes = [vp, C.POINTER(Camera), C.POINTER(Env), C.POINTER(RenderOpts), vp, u32, u32]
     L.vx_bounce_rays.argtypes = [vp, C.POINTER(Camera), C.POINTER(RenderOpts), u32, u32, vp, vp, vp, vp, vp]
     L.vx_tracer_set_timing.argtypes = [vp, i32]
@@ -287,6 +289,13 @@ class World:
 
     def save(self, path):
         _check(lib().vx_world_save(self.h, os.fsencode(path)))
+
+    def render_static(self, cam, env, opts, d_bgra, W, H, d_steps=0, stream=0):
+        """vx_render_static: VoxelRaytracer3D.render_device without a tracer and without any allocation (the frame's scratch is
+        a fixed device array of the library; frames up to STATIC_MAX_RAY_IDS ray ids, e.g. 640x360; cam.tan_half must be set;
+        calls that overlap on the GPU race).  No counterpart in the reference."""
+        _check(lib().vx_render_static(self.h, C.byref(cam), C.byref(env), C.byref(opts), int(d_bgra), int(d_steps) or None, W, H,
+                                      int(stream) or None))
 
     def edit(self, voxels, solid=True):
         """Set (or clear) the voxels (n x 3 integer coordinates) in place: masks, bounds and top-level bits of the touched

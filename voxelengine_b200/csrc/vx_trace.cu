@@ -1054,6 +1054,112 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     return VX_OK;
 }
 
+// ---- vx_render_static: the shadowed frame of vx_render for callers that may not allocate -----------------------------------
+// No counterpart in the reference; added (CUDA graph capture, serving loops and harnesses
+// that forbid cudaMalloc).  Everything vx_render keeps in a tracer's cudaMalloc'd buffers — the three ray / queue counters and the
+// queue of primary hits waiting for their sun ray (record, aux words, saved lane state: 72 bytes per ray id) — lives in ONE
+// file-scope device array of fixed size; every GPU that loads the library holds it until exit.  The kernels are vx_render's own.
+constexpr unsigned long long kStaticMaxIds = VX_STATIC_MAX_RAY_IDS; // ray ids per call (128 per 16x8 pixel tile: 640x360 = 230400)
+constexpr size_t kStaticHeader = 256;                               // counters: frame queue count, primary ray counter, sun ray counter
+constexpr size_t kStaticRecOff = kStaticHeader;
+constexpr size_t kStaticAuxOff = kStaticRecOff + (size_t)kStaticMaxIds * sizeof(float4);
+constexpr size_t kStaticLanesOff = kStaticAuxOff + (size_t)kStaticMaxIds * 2u * sizeof(uint32_t);
+constexpr size_t kStaticBytes = kStaticLanesOff + (size_t)kStaticMaxIds * 3u * sizeof(uint4);
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+namespace {
+struct StaticDevice { unsigned char* base = nullptr; int sm_count = 0; bool ready = false; };
+constexpr int kStaticMaxDevices = 64;
+StaticDevice g_static_device[kStaticMaxDevices];
+std::mutex g_static_mu;
+
+// Once per device, with that device current: in host code `g_static_scratch` is only a stand-in for the symbol, the address the
+// kernels need comes from cudaGetSymbolAddress.
+int static_setup(int device, StaticDevice& out) {
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    VX_REQUIRE(device >= 0 && device < kStaticMaxDevices, "vx_render_static: device index out of range");
+    StaticDevice& d = g_static_device[device];
+    if (!d.ready) {
+        void* p = nullptr;
+        VX_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        VX_REQUIRE(p != nullptr, "vx_render_static: cudaGetSymbolAddress returned NULL");
+        VX_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, device));
+        d.base = (unsigned char*)p;
+        d.ready = true;
+    }
+    out = d;
+    return VX_OK;
+}
+} // namespace
+
+extern "C" int vx_render_static(const vx_world* world, const vx_camera* cam, const vx_env* env, const vx_render_opts* opts, void* d_bgra,
+                                int32_t* d_steps, uint32_t W, uint32_t H, void* stream) {
+    VX_REQUIRE(world && cam && env && opts && d_bgra, "NULL argument");
+    VX_REQUIRE(opts->norm_mode == VX_NORM_DEVICE || opts->norm_mode == VX_NORM_HOST, "render supports VX_NORM_DEVICE or VX_NORM_HOST");
+    VX_REQUIRE(opts->d_stats == nullptr, "vx_render_static: the counting kernels (d_stats) need a tracer; use vx_render");
+    VX_REQUIRE(cam->tan_half > 0.0f, "vx_render_static: pass cam->tan_half (vx_device_tanf, once at set-up); evaluating it here would allocate");
+    DeviceGuard guard(world->device);
+    if (!guard.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+    StaticDevice sd;
+    int rc = static_setup(world->device, sd);
+    if (rc) return rc;
+    vx_tracer local;  // plain host struct (no device state): what fill_frame and persistent_blocks read
+    local.world = const_cast<vx_world*>(world); local.device = world->device; local.sm_count = sd.sm_count;
+    FrameParams f;
+    rc = fill_frame(&local, cam, env, opts, W, H, f);
+    if (rc) return rc;
+    if (f.tw == 0 || f.th == 0) return VX_OK;
+    const uint32_t bands = (f.th + 7u) / 8u;
+    const uint32_t my_bands = bands > f.band_index ? (bands - f.band_index + f.band_count - 1u) / f.band_count : 0u;
+    if (my_bands == 0) return VX_OK;
+#if VX_TILE_SHAPE == 2
+    f.mcols = (f.tw + 31u) / 32u * 2u;
+#else
+    f.mcols = (f.tw + 15u) / 16u;
+#endif
+    f.ids = (unsigned long long)f.mcols * my_bands * 128ull;
+    if (f.ids > kStaticMaxIds) {
+        char msg[256];
+        snprintf(msg, sizeof msg, "vx_render_static: this frame needs %llu ray ids, the static scratch holds VX_STATIC_MAX_RAY_IDS = %llu "
+                 "(e.g. 640x360); render it in tiles or bands, or use vx_render", f.ids, kStaticMaxIds);
+        set_error(msg);
+        return VX_ERR_INVALID;
+    }
+    f.tile_trace = nullptr;
+    const WorldView w = world->view();
+    cudaStream_t cs = (cudaStream_t)stream;
+    // the array keeps the last call's contents: the three counters must start at zero, the queue entries are written before read
+    VX_CUDA(cudaMemsetAsync(sd.base, 0, kStaticHeader, cs));
+    unsigned long long* counters = (unsigned long long*)sd.base;
+    ShadowQueue q{nullptr, nullptr, nullptr, nullptr};
+    const bool shadow_pass = opts->shadows && !opts->debug_view;
+    if (shadow_pass) {
+        q.rec = (float4*)(sd.base + kStaticRecOff); q.aux = (uint32_t*)(sd.base + kStaticAuxOff); q.lanes = (uint4*)(sd.base + kStaticLanesOff);
+        q.count = counters;
+    }
+    unsigned long long *next1 = counters + 8, *next2 = counters + 16;
+    unsigned blocks = 1;
+    const unsigned dense_blocks = (unsigned)(sd.sm_count > 0 ? sd.sm_count : 148) * 8u;
+#define VX_LAUNCH(N) do { \
+        if (f.ortho_w > 0.0f) { \
+            rc = persistent_blocks(&local, primary_rays<N, false, true>, f.ids, blocks); if (rc) return rc; \
+            primary_rays<N, false, true><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, nullptr, q, next1); \
+        } else { \
+            rc = persistent_blocks(&local, primary_rays<N, false, false>, f.ids, blocks); if (rc) return rc; \
+            primary_rays<N, false, false><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, nullptr, q, next1); \
+        } \
+        if (shadow_pass) { \
+            shadow_setup<N, false><<<dense_blocks * (256 / VX_SETUP_THREADS), VX_SETUP_THREADS, 0, cs>>>(w, f, q); \
+            rc = persistent_blocks(&local, shadow_rays<N, false, false>, f.ids, blocks); if (rc) return rc; \
+            shadow_rays<N, false, false><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, q, next2); \
+            shade_pixels<N, false><<<dense_blocks, 256, 0, cs>>>(f, (uint8_t*)d_bgra, d_steps, nullptr, q); \
+        } } while (0)
+    if (opts->norm_mode == VX_NORM_HOST) VX_LAUNCH(1); else VX_LAUNCH(0);
+#undef VX_LAUNCH
+    VX_CUDA(cudaGetLastError());
+    return VX_OK;
+}
+
 extern "C" int vx_bounce_rays(vx_tracer* t, const vx_camera* cam, const vx_render_opts* opts, uint32_t W, uint32_t H, float* d_origins,
                               float* d_dirs, uint32_t* d_pixels, unsigned long long* d_count, void* stream) {
     VX_REQUIRE(t && cam && opts && d_origins && d_dirs && d_pixels && d_count, "NULL argument");
