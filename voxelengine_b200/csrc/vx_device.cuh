@@ -68,6 +68,7 @@ __device__ __forceinline__ uint32_t tiled_index(int x, int y, int z, uint32_t ti
 // is vx_march.cuh.
 // ---------------------------------------------------------------------------------------------
 struct Ray {
+    bool dnz, dpos;        // every component of d finite and not zero / and positive (vx_march.cuh F_DNZ, F_DPOS)
     V3 d;
     float ivx, ivy, ivz;   // slab test: 1/(d == 0 ? FLT_EPS : d)          VolumeRaytracer.cu:127-129
     float dtx, dty, dtz;   // |1/d| or +inf                                :199-201
@@ -75,6 +76,7 @@ struct Ray {
 };
 __device__ __forceinline__ Ray make_ray(V3 d) {
     Ray r;
+    r.dnz = false; r.dpos = false;
     r.d = d;
     r.ivx = fdiv(1.0f, d.x == 0.0f ? kFltEps : d.x);
     r.ivy = fdiv(1.0f, d.y == 0.0f ? kFltEps : d.y);

@@ -26,6 +26,26 @@ constexpr uint32_t F_HIT = 1u << 6;
 constexpr uint32_t F_SHADOW = 1u << 7; // render: this lane marches the shadow ray of its pixel
 constexpr int F_SN_SHIFT = 8;          // bits 8-10: normal code of the grid-entry clip (start_normal)
 constexpr uint32_t F_NEAR = 1u << 11;  // the kMaxSteps cap can be reached before the border: the fast loop checks per chunk
+constexpr uint32_t F_DNZ = 1u << 12;   // every direction component is finite and not zero: the tMax divisions need no guard
+constexpr uint32_t F_DPOS = 1u << 13;  // ... and positive (the sun rays of the reference's light): then face - s = trunc(s) + 1 - s is never zero either
+
+// Round-2 trims of the per-brick chain (slab test -> brick march -> re-seed -> traversal start); each can be switched off
+// (-DVX_OPT_x=0) to measure it.  None changes a result bit.
+#ifndef VX_OPT_TDIV
+#define VX_OPT_TDIV 1  // tMax divisions: no d != 0 guard for F_DNZ rays, zero numerators answered without div.rn's slow path
+#endif
+#ifndef VX_OPT_NEXT
+#define VX_OPT_NEXT 1  // nextafterf(x, +-inf) of the re-seeding nudge as an integer step on the bits
+#endif
+#ifndef VX_OPT_CSTEP
+#define VX_OPT_CSTEP 1 // the step after a slab miss of a fast-mode traversal: the fast loop's predicated step
+#endif
+#ifndef VX_OPT_FMA
+#define VX_OPT_FMA 1   // tight-box corners as one exact FMA each
+#endif
+#ifndef VX_OPT_DPOS
+#define VX_OPT_DPOS 1  // F_DPOS rays: plain divisions
+#endif
 
 // Axis-aligned unit normals as a 3-bit code: 0 = (0,0,0); 1 + 2*axis + (negative ? 1 : 0).
 __device__ __forceinline__ V3 normal_from_code(uint32_t c) {
@@ -55,6 +75,7 @@ __device__ __forceinline__ void lane_set_state(Lane& L, uint32_t st) { L.flags =
 __device__ __forceinline__ float lane_dt(float d, float iv) { return d != 0.0f ? fabsf(iv) : CUDART_INF_F; } // :199-201
 __device__ __forceinline__ Ray lane_ray(const Lane& L) {
     Ray r;
+    r.dnz = (L.flags & F_DNZ) != 0u; r.dpos = (L.flags & F_DPOS) != 0u;
     r.d = L.d; r.ivx = L.ivx; r.ivy = L.ivy; r.ivz = L.ivz;
     r.dtx = lane_dt(L.d.x, L.ivx); r.dty = lane_dt(L.d.y, L.ivy); r.dtz = lane_dt(L.d.z, L.ivz);
     r.sx = L.d.x > 0.0f ? 1 : -1; r.sy = L.d.y > 0.0f ? 1 : -1; r.sz = L.d.z > 0.0f ? 1 : -1;
@@ -87,6 +108,29 @@ __device__ __forceinline__ V3 to_brick_units(const WorldView& w, V3 p) {
     return mk(fdiv(p.x, ff), fdiv(p.y, ff), fdiv(p.z, ff));
 }
 
+// tMax = (face - s) / d (VolumeRaytracer.cu:206-214) for a direction component that is finite and not zero (F_DNZ).
+// A zero numerator — the start lies exactly on the face it is measured to: every brick entered through an upper face of
+// its tight box by a ray that descends along that axis, every camera on an integer brick coordinate — gives (+-0) / d, a
+// zero with the XOR of the signs.  div.rn's in-line path does not take zero operands (FCHK sends them through a
+// 40-instruction routine, 2.7 % of primary_rays' instructions at the benchmark camera), so that case is answered here and
+// the division runs on a stand-in numerator.
+__device__ __forceinline__ float tmax_div(float a, float d) {
+    const bool z = a == 0.0f;
+    const float q = fdiv(z ? 1.0f : a, d);
+    return z ? __uint_as_float((__float_as_uint(a) ^ __float_as_uint(d)) & 0x80000000u) : q;
+}
+__device__ __forceinline__ bool finite_nonzero(float v) { return (__float_as_uint(v) & 0x7FFFFFFFu) - 1u < 0x7F7FFFFFu; }
+
+// nextafterf(x, down ? -inf : +inf) (the nudge of VolumeRaytracer.cu:457-459).  For a finite x that is neither zero nor
+// the largest float it is one step on the bit pattern, away from zero or towards it; everything else goes to the library.
+__device__ __forceinline__ float next_toward(float x, bool down) {
+#if VX_OPT_NEXT
+    const uint32_t b = __float_as_uint(x);
+    if ((b & 0x7FFFFFFFu) - 1u < 0x7F7FFFFEu) return __uint_as_float(down == (bool)(b >> 31) ? b + 1u : b - 1u);
+#endif
+    return nextafterf(x, down ? -CUDART_INF_F : CUDART_INF_F);
+}
+
 // Ray set-up shared by primary, shadow and batch rays: slab inverses, grid-entry clip (VolumeRaytracer.cu:361-381).
 // `s` is origin / factor, `d` the normalised direction.
 __device__ __forceinline__ void lane_setup(const WorldView& w, Lane& L, V3 s, V3 d, uint32_t keep_flags) {
@@ -107,18 +151,33 @@ __device__ __forceinline__ void lane_setup(const WorldView& w, Lane& L, V3 s, V3
     L.total = 0; L.csteps = 0; L.fsteps = 0; L.fcell = 0;
     L.work.C = L.work.K = L.work.E = 0;
     L.flags = keep_flags | (sn << F_SN_SHIFT) | ST_BEGIN;
+    if (VX_OPT_TDIV && finite_nonzero(d.x) && finite_nonzero(d.y) && finite_nonzero(d.z))
+        L.flags |= F_DNZ | ((VX_OPT_DPOS && d.x > 0.0f && d.y > 0.0f && d.z > 0.0f) ? F_DPOS : 0u);
 }
 
 // Start of one coarse DDARayTraversal (VolumeRaytracer.cu:186-232) from L.s; also the `while (total_steps <
 // maxSteps)` test of Raytrace (:383).
+// SUN: the caller's rays share one direction (sun rays), so the F_DPOS test is warp-uniform and worth a code path of its own;
+// kernels with mixed directions do not carry it (compiled into primary_rays it costs 5 % without ever being taken).
+template <bool SUN>
 __device__ __forceinline__ void lane_begin(const WorldView& w, Lane& L, int max_steps) {
     L.flags &= ~(F_SLOW | F_EDGE | F_CAPOK | F_NEAR);
     if (!(L.total < max_steps)) { lane_set_state(L, ST_DONE); return; }
     const int x0 = (int)L.s.x, y0 = (int)L.s.y, z0 = (int)L.s.z; // cvt.rzi: truncation, saturating, NaN -> 0
     const int ox = L.d.x > 0.0f, oy = L.d.y > 0.0f, oz = L.d.z > 0.0f;
-    L.tx = L.d.x != 0.0f ? fdiv(fsub((float)(x0 + ox), L.s.x), L.d.x) : CUDART_INF_F;
-    L.ty = L.d.y != 0.0f ? fdiv(fsub((float)(y0 + oy), L.s.y), L.d.y) : CUDART_INF_F;
-    L.tz = L.d.z != 0.0f ? fdiv(fsub((float)(z0 + oz), L.s.z), L.d.z) : CUDART_INF_F;
+    if (VX_OPT_DPOS && SUN && (L.flags & F_DPOS)) {
+        L.tx = fdiv(fsub((float)(x0 + 1), L.s.x), L.d.x);
+        L.ty = fdiv(fsub((float)(y0 + 1), L.s.y), L.d.y);
+        L.tz = fdiv(fsub((float)(z0 + 1), L.s.z), L.d.z);
+    } else if (L.flags & F_DNZ) {
+        L.tx = tmax_div(fsub((float)(x0 + ox), L.s.x), L.d.x);
+        L.ty = tmax_div(fsub((float)(y0 + oy), L.s.y), L.d.y);
+        L.tz = tmax_div(fsub((float)(z0 + oz), L.s.z), L.d.z);
+    } else {
+        L.tx = L.d.x != 0.0f ? fdiv(fsub((float)(x0 + ox), L.s.x), L.d.x) : CUDART_INF_F;
+        L.ty = L.d.y != 0.0f ? fdiv(fsub((float)(y0 + oy), L.s.y), L.d.y) : CUDART_INF_F;
+        L.tz = L.d.z != 0.0f ? fdiv(fsub((float)(z0 + oz), L.s.z), L.d.z) : CUDART_INF_F;
+    }
     // cells in [-1, dim] have a bordered index; anything else fails the first bounds test with zero steps (:283-287)
     if (!((unsigned)(x0 + 1) <= (unsigned)(w.cx + 1) && (unsigned)(y0 + 1) <= (unsigned)(w.cy + 1) &&
           (unsigned)(z0 + 1) <= (unsigned)(w.cz + 1))) { lane_set_state(L, ST_DONE); return; }
@@ -147,6 +206,26 @@ __device__ __forceinline__ void lane_step(const WorldView& w, Lane& L) {
     L.tx = mx ? tn : L.tx; L.ty = my ? tn : L.ty; L.tz = mz ? tn : L.tz;
     const int dix = L.d.x > 0.0f ? 1 : -1, diy = L.d.y > 0.0f ? w.pnx : -w.pnx, diz = L.d.z > 0.0f ? w.pnxy : -w.pnxy;
     L.idx += (uint32_t)(mx ? dix : (my ? diy : diz));
+}
+
+// One fast-loop step.  With no NaN among the tMax values (F_CAPOK) the reference's comparison chain (:293-322) picks the
+// axis of the minimum with ties z over y over x, and the chosen axis' tMax IS that minimum, so "tMax[axis] += tDelta[axis]"
+// under the axis predicate is the reference's add.  Written as predicated adds (FMA pipe) because the select-based form
+// the compiler prefers is bound by the half-rate ALU pipe (profiles/).
+__device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint32_t& idx, float dtx, float dty, float dtz, int dix, int diy,
+                                          int diz) {
+    asm("{\n\t.reg .pred pz, py, px;\n\t.reg .f32 m;\n\t"
+        "min.f32 m, %0, %1;\n\t"
+        "setp.le.f32 pz, %2, m;\n\t"
+        "setp.le.and.f32 py|px, %1, %0, !pz;\n\t" // py = (ty <= tx) & !pz, px = !(ty <= tx) & !pz
+        "@pz add.rn.f32 %2, %2, %6;\n\t"
+        "@py add.rn.f32 %1, %1, %5;\n\t"
+        "@px add.rn.f32 %0, %0, %4;\n\t"
+        "@pz add.s32 %3, %3, %9;\n\t"
+        "@py add.s32 %3, %3, %8;\n\t"
+        "@px add.s32 %3, %3, %7;\n\t}"
+        : "+f"(tx), "+f"(ty), "+f"(tz), "+r"(idx)
+        : "f"(dtx), "f"(dty), "f"(dtz), "r"(dix), "r"(diy), "r"(diz));
 }
 
 #ifndef VX_REFILL_MIN
@@ -387,13 +466,25 @@ __device__ __forceinline__ void fine_step(float& tx, float& ty, float& tz, uint3
         : "f"(dtx), "f"(dty), "f"(dtz));
 }
 
+template <bool SUN>
 __device__ __forceinline__ bool fine_march8_quick(const uint32_t* __restrict__ mask, V3 s, const Ray& r, FineOut& o) {
     int cx = (int)s.x, cy = (int)s.y, cz = (int)s.z;
     if ((unsigned)cx > 8u || (unsigned)cy > 8u || (unsigned)cz > 8u) { VX_FSTAT(1); return false; }
     const int ox = r.sx > 0, oy = r.sy > 0, oz = r.sz > 0;
-    float tx = r.d.x != 0.0f ? fdiv(fsub((float)(cx + ox), s.x), r.d.x) : CUDART_INF_F;
-    float ty = r.d.y != 0.0f ? fdiv(fsub((float)(cy + oy), s.y), r.d.y) : CUDART_INF_F;
-    float tz = r.d.z != 0.0f ? fdiv(fsub((float)(cz + oz), s.z), r.d.z) : CUDART_INF_F;
+    float tx, ty, tz;
+    if (VX_OPT_DPOS && SUN && r.dpos) {
+        tx = fdiv(fsub((float)(cx + 1), s.x), r.d.x);
+        ty = fdiv(fsub((float)(cy + 1), s.y), r.d.y);
+        tz = fdiv(fsub((float)(cz + 1), s.z), r.d.z);
+    } else if (r.dnz) {
+        tx = tmax_div(fsub((float)(cx + ox), s.x), r.d.x);
+        ty = tmax_div(fsub((float)(cy + oy), s.y), r.d.y);
+        tz = tmax_div(fsub((float)(cz + oz), s.z), r.d.z);
+    } else {
+        tx = r.d.x != 0.0f ? fdiv(fsub((float)(cx + ox), s.x), r.d.x) : CUDART_INF_F;
+        ty = r.d.y != 0.0f ? fdiv(fsub((float)(cy + oy), s.y), r.d.y) : CUDART_INF_F;
+        tz = r.d.z != 0.0f ? fdiv(fsub((float)(cz + oz), s.z), r.d.z) : CUDART_INF_F;
+    }
     VX_FSTAT(0);
     const float t_first = fminf(fminf(tx, ty), tz);
     int pre = 0; // steps taken before the loop (out of a virtual cell on the far face)
@@ -509,9 +600,9 @@ __device__ __forceinline__ void brick_done(const WorldView& w, Lane& L, const Fi
     }
     V3 start = to_brick_units(w, hit_pos);
     if (q.oob && qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) { // :438-489
-        start.x = nextafterf(start.x, L.d.x < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
-        start.y = nextafterf(start.y, L.d.y < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
-        start.z = nextafterf(start.z, L.d.z < 0.0f ? -CUDART_INF_F : CUDART_INF_F);
+        start.x = next_toward(start.x, L.d.x < 0.0f);
+        start.y = next_toward(start.y, L.d.y < 0.0f);
+        start.z = next_toward(start.z, L.d.z < 0.0f);
         if (qx == (int)start.x && qy == (int)start.y && qz == (int)start.z) {
             // NextCell of the COARSE traversal = the cell after its final advance (:347, :473)
             const int sx = L.d.x > 0.0f ? 1 : -1, sy = L.d.y > 0.0f ? 1 : -1, sz = L.d.z > 0.0f ? 1 : -1;
@@ -530,7 +621,7 @@ __device__ __forceinline__ void brick_done(const WorldView& w, Lane& L, const Fi
 // ST_CAND: the occupied cell L.bidx.  Tight-AABB slab test (VolumeRaytracer.cu:248-273); on a hit the brick is
 // marched (:409-436) and the lane either finishes (ST_DONE + F_HIT, result in pos/ncode) or re-seeds its start
 // (:438-489) and goes back to ST_BEGIN; on a slab miss it takes the step the reference takes and keeps going.
-template <bool BATCH, bool COUNT>
+template <bool BATCH, bool COUNT, bool SUN>
 __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, uint32_t& ncode) {
     int qx, qy, qz;
     cell_of(w, L.bidx, qx, qy, qz);
@@ -551,7 +642,13 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
     const float l0 = (float)(b & 31u), l1 = (float)((b >> 5) & 31u), l2 = (float)((b >> 10) & 31u);
     const float h0 = (float)(((b >> 15) & 31u) + 1u), h1 = (float)(((b >> 20) & 31u) + 1u), h2 = (float)(((b >> 25) & 31u) + 1u);
     V3 lo, hi;
-    if (w.inv_factor != 0.0f) { // x / 2^k == x * 2^-k exactly
+    if (VX_OPT_FMA && w.inv_factor >= 0.00390625f) {
+        // factor = 2^k <= 256: l / factor + q = (l + q * factor) / factor with l <= 32 and q < 2^16 is a float, so neither the
+        // product nor the sum rounds and one FMA gives the reference's two operations bit for bit
+        const float inv_f = w.inv_factor;
+        lo = mk(__fmaf_rn(l0, inv_f, (float)qx), __fmaf_rn(l1, inv_f, (float)qy), __fmaf_rn(l2, inv_f, (float)qz));
+        hi = mk(__fmaf_rn(h0, inv_f, (float)qx), __fmaf_rn(h1, inv_f, (float)qy), __fmaf_rn(h2, inv_f, (float)qz));
+    } else if (w.inv_factor != 0.0f) { // x / 2^k == x * 2^-k exactly
         const float inv_f = w.inv_factor;
         lo = mk(fadd(fmul(l0, inv_f), (float)qx), fadd(fmul(l1, inv_f), (float)qy), fadd(fmul(l2, inv_f), (float)qz));
         hi = mk(fadd(fmul(h0, inv_f), (float)qx), fadd(fmul(h1, inv_f), (float)qy), fadd(fmul(h2, inv_f), (float)qz));
@@ -562,6 +659,11 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
     }
     const Slab sl = ray_aabb(L.s, r, lo, hi);
     if (!sl.hit) {
+        if (VX_OPT_CSTEP && !(L.flags & F_SLOW)) { // fast mode: no NaN among the tMax values, so the fast loop's step is the reference's
+            fast_step(L.tx, L.ty, L.tz, L.idx, r.dtx, r.dty, r.dtz, r.sx, L.d.y > 0.0f ? w.pnx : -w.pnx, L.d.z > 0.0f ? w.pnxy : -w.pnxy);
+            lane_set_state(L, ST_FAST);
+            return;
+        }
         lane_step(w, L);
         lane_set_state(L, (L.flags & F_SLOW) ? ST_SLOW : ST_FAST);
         return;
@@ -590,30 +692,10 @@ __device__ __forceinline__ void lane_cand(const WorldView& w, Lane& L, V3& pos, 
         if (L.flags & F_CAPOK) fine_march8(mask, local, r, q);
         else fine_march<true>(mask, 8, local, r, q);
 #else
-        if (!((L.flags & F_CAPOK) && fine_march8_quick(mask, local, r, q))) fine_march<true>(mask, 8, local, r, q);
+        if (!((L.flags & F_CAPOK) && fine_march8_quick<SUN>(mask, local, r, q))) fine_march<true>(mask, 8, local, r, q);
 #endif
     } else fine_march<false>(mask, w.factor, local, r, q);
     brick_done<BATCH>(w, L, q, qx, qy, qz, cx, cy, cz, next_axis, q.steps == 0 ? sl.ncode : q.ncode, pos, ncode);
-}
-
-// One fast-loop step.  With no NaN among the tMax values (F_CAPOK) the reference's comparison chain (:293-322) picks the
-// axis of the minimum with ties z over y over x, and the chosen axis' tMax IS that minimum, so "tMax[axis] += tDelta[axis]"
-// under the axis predicate is the reference's add.  Written as predicated adds (FMA pipe) because the select-based form
-// the compiler prefers is bound by the half-rate ALU pipe (profiles/).
-__device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint32_t& idx, float dtx, float dty, float dtz, int dix, int diy,
-                                          int diz) {
-    asm("{\n\t.reg .pred pz, py, px;\n\t.reg .f32 m;\n\t"
-        "min.f32 m, %0, %1;\n\t"
-        "setp.le.f32 pz, %2, m;\n\t"
-        "setp.le.and.f32 py|px, %1, %0, !pz;\n\t" // py = (ty <= tx) & !pz, px = !(ty <= tx) & !pz
-        "@pz add.rn.f32 %2, %2, %6;\n\t"
-        "@py add.rn.f32 %1, %1, %5;\n\t"
-        "@px add.rn.f32 %0, %0, %4;\n\t"
-        "@pz add.s32 %3, %3, %9;\n\t"
-        "@py add.s32 %3, %3, %8;\n\t"
-        "@px add.s32 %3, %3, %7;\n\t}"
-        : "+f"(tx), "+f"(ty), "+f"(tz), "+r"(idx)
-        : "f"(dtx), "f"(dty), "f"(dtz), "r"(dix), "r"(diy), "r"(diz));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -625,6 +707,7 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 //   void finish(w, L, pos, ncode)         consume a finished march and set the lane ST_IDLE (or re-arm it)
 //   void flush()                          called by all 32 lanes whenever the whole warp is idle (before a refill / the end)
 //   kRefill                               idle lanes that trigger a refill (32: whole tiles only)
+//   kSun                                  all rays share one direction (see lane_begin)
 //   kFastQuad, kLeaveNum, kLeaveDen       fast-loop scheduling, see lane_fast
 //   kDrain, void drain(uint32_t done)     kDrain: called by all 32 lanes once per round, after finish(), with the ballot of the
 //                                         lanes that finished this round (a policy batching its per-ray epilogue across the warp);
@@ -680,10 +763,10 @@ __device__ __forceinline__ void run_lanes(const WorldView& w, Policy& pol, unsig
     for (;;) {
         V3 pos = mk(0.0f, 0.0f, 0.0f);
         uint32_t ncode = 0;
-        if (lane_state(L) == ST_BEGIN) lane_begin(w, L, max_steps);
+        if (lane_state(L) == ST_BEGIN) lane_begin<Policy::kSun>(w, L, max_steps);
         if (lane_state(L) == ST_FAST) lane_fast<COUNT, Policy::kFastQuad, Policy::kLeaveNum, Policy::kLeaveDen>(w, L);
         if (lane_state(L) == ST_SLOW) lane_slow<COUNT>(w, L);
-        if (lane_state(L) == ST_CAND) lane_cand<BATCH, COUNT>(w, L, pos, ncode);
+        if (lane_state(L) == ST_CAND) lane_cand<BATCH, COUNT, Policy::kSun>(w, L, pos, ncode);
         if constexpr (Policy::kDrain) {
             const uint32_t done = __ballot_sync(kFull, lane_state(L) == ST_DONE);
             pol.done_ballot = done; // finish() places its result by rank within this ballot, not by whoever happens to be converged

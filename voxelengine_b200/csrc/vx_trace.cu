@@ -45,7 +45,7 @@ struct BatchPolicy {
     HitPlanes out;
     unsigned long long id; // per lane: the ray being marched
     static constexpr int kRefill = VX_REFILL_MIN;
-    static constexpr bool kDrain = false;
+    static constexpr bool kDrain = false, kSun = false;
     static constexpr int kFastQuad = VX_BATCH_QUAD, kLeaveNum = VX_BATCH_LEAVE_NUM, kLeaveDen = VX_BATCH_LEAVE_DEN;
 
     __device__ __forceinline__ unsigned long long count() const { return n; }
@@ -223,7 +223,7 @@ __device__ __forceinline__ void emit_pixel(const FrameParams& f, bool ortho, uin
 
 template <int NORM, bool STATS, bool ORTHO>
 struct PrimaryPolicy {
-    static constexpr bool kDrain = false;
+    static constexpr bool kDrain = false, kSun = false;
     static constexpr int kFastQuad = VX_PRIMARY_QUAD, kLeaveNum = VX_PRIMARY_LEAVE_NUM, kLeaveDen = VX_PRIMARY_LEAVE_DEN;
     static constexpr int kRefill = 32; // a warp takes a whole tile at a time: neighbouring rays stay in step (2.2 ms instead of
                                        // 1.56 ms per 4K frame with 16..28), and flush() relies on it
@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(VX_SETUP_THREADS, VX_SETUP_MIN_BLOCKS) shadow_
         Lane L;
         lane_setup(w, L, to_brick_units(w, so), d, F_SHADOW);
         L.tx = L.ty = L.tz = 0.0f; L.idx = 0; L.bidx = 0;
-        lane_begin(w, L, kMaxSteps);
+        lane_begin<true>(w, L, kMaxSteps);
         // A sun ray starts just off a surface, i.e. inside an occupied brick: its first examination finds that brick, and the
         // march through it (a handful of voxel steps, much the same for the neighbouring pixels that sit next to each other
         // in the queue) is done here, with all lanes busy, and so is the start of the traversal that follows.  shadow_rays
@@ -375,8 +375,8 @@ __global__ void __launch_bounds__(VX_SETUP_THREADS, VX_SETUP_MIN_BLOCKS) shadow_
         if (lane_state(L) == ST_FAST && cell_bit(w.ptop, L.idx)) { L.bidx = L.idx; lane_set_state(L, ST_CAND); }
         if (lane_state(L) == ST_CAND) {
             V3 pos; uint32_t ncode;
-            lane_cand<false, STATS>(w, L, pos, ncode);
-            if (lane_state(L) == ST_BEGIN) lane_begin(w, L, kMaxSteps);
+            lane_cand<false, STATS, true>(w, L, pos, ncode);
+            if (lane_state(L) == ST_BEGIN) lane_begin<true>(w, L, kMaxSteps);
         }
         q.lanes[3 * i] = make_uint4(__float_as_uint(L.s.x), __float_as_uint(L.s.y), __float_as_uint(L.s.z), __float_as_uint(L.tx));
         q.lanes[3 * i + 1] = make_uint4(__float_as_uint(L.ty), __float_as_uint(L.tz), L.idx, (uint32_t)L.total);
@@ -396,7 +396,7 @@ constexpr uint32_t kShadeList = 64; // per warp: fewer than 32 waiting + at most
 template <int NORM, bool STATS, bool FUSE>
 struct ShadowPolicy {
     static constexpr int kRefill = VX_SHADOW_REFILL;
-    static constexpr bool kDrain = FUSE;
+    static constexpr bool kDrain = FUSE, kSun = true;
     static constexpr int kFastQuad = VX_SHADOW_QUAD, kLeaveNum = VX_SHADOW_LEAVE_NUM, kLeaveDen = VX_SHADOW_LEAVE_DEN;
     const FrameParams& f;
     ShadowQueue q;
