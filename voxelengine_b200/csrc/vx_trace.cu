@@ -88,9 +88,18 @@ struct BatchPolicy {
     }
 };
 
-template <int NORM, bool COUNT>
-__global__ void __launch_bounds__(128, VX_TRACE_MIN_BLOCKS) trace_rays(WorldView w, const float* __restrict__ origins, const float* __restrict__ dirs,
+// F8 (every march kernel): the world's bricks are 8^3, known at compile time.  The kernels for any other factor carry the generic
+// brick march, nine IEEE divisions by the factor and the loads of the three factor-dependent constants; the march kernels are
+// instruction-fetch sensitive (58 KB of code, `no_instruction` stalls), so the common case gets kernels without that code.
+__device__ __forceinline__ WorldView factor8_view(WorldView w) {
+    w.factor = 8; w.inv_factor = 0.125f; w.words_per_brick = 16u;
+    return w;
+}
+
+template <int NORM, bool COUNT, bool F8>
+__global__ void __launch_bounds__(128, VX_TRACE_MIN_BLOCKS) trace_rays(WorldView w_in, const float* __restrict__ origins, const float* __restrict__ dirs,
                                                   unsigned long long n, int max_steps, HitPlanes out, unsigned long long* next) {
+    const WorldView w = F8 ? factor8_view(w_in) : w_in;
     BatchPolicy<NORM, COUNT> pol;
     pol.origins = origins; pol.dirs = dirs; pol.n = n; pol.cap = max_steps; pol.out = out; pol.id = 0;
     run_lanes<true, COUNT>(w, pol, next);
@@ -192,12 +201,13 @@ __device__ __forceinline__ void add_stats(unsigned long long* __restrict__ stats
 }
 
 // Everything screenDispatch does once the rays of a pixel are known (Renderer.cu:203-275).
-template <int NORM>
+// PLAIN: the caller only ever has misses to write and the debug view is off (primary_rays of a shadowed frame): no shading code.
+template <int NORM, bool PLAIN = false>
 __device__ __forceinline__ void emit_pixel(const FrameParams& f, bool ortho, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane, uint32_t pix,
                                            bool hit, V3 pos, uint32_t ncode, bool shadowed, int steps, V3 miss_dir) {
     const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
     const int W = (int)f.W, H = (int)f.H;
-    if (hit) {
+    if (!PLAIN && hit) {
         const V3 nn = normal_from_code(ncode);
         const V3 n = mk(-nn.x, -nn.y, -nn.z);
         const V3 cam = pixel_origin(f, ortho, x, y);
@@ -217,11 +227,13 @@ __device__ __forceinline__ void emit_pixel(const FrameParams& f, bool ortho, uin
         put_pixel(bgra, f.W, f.H, x, y, miss_dir); // miss: colour = ray direction, Renderer.cu:254-258
     }
     if (pix & (1u << 30)) put_pixel(bgra, f.W, f.H, x, y, mk(10.0f, 10.0f, 10.0f)); // crosshair, :260-268
-    if (f.debug_view && x < (W >> 1) && y > (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(fdiv((float)steps, 256.0f), 0.0f, 0.0f));
+    if (!PLAIN && f.debug_view && x < (W >> 1) && y > (H >> 1)) put_pixel(bgra, f.W, f.H, x, y, mk(fdiv((float)steps, 256.0f), 0.0f, 0.0f));
     if (steps_plane) steps_plane[(size_t)y * f.W + x] = steps;
 }
 
-template <int NORM, bool STATS, bool ORTHO>
+// QUEUED: the launch is the first of a shadowed frame (shadows on, debug view off), known at compile time: every hit goes to
+// the frame's queue and this kernel shades nothing.
+template <int NORM, bool STATS, bool ORTHO, bool QUEUED>
 struct PrimaryPolicy {
     static constexpr bool kDrain = false, kSun = false;
     static constexpr int kFastQuad = VX_PRIMARY_QUAD, kLeaveNum = VX_PRIMARY_LEAVE_NUM, kLeaveDen = VX_PRIMARY_LEAVE_DEN;
@@ -322,7 +334,7 @@ struct PrimaryPolicy {
 
     __device__ __forceinline__ void finish(const WorldView& w, Lane& L, V3 pos, uint32_t ncode) {
         const bool hit = L.flags & F_HIT;
-        const bool queued = hit && !f.debug_view && f.shadows; // the shadow Raytrace of Renderer.cu:102 runs in shadow_rays
+        const bool queued = QUEUED ? hit : (hit && !f.debug_view && f.shadows); // the shadow Raytrace of Renderer.cu:102 runs in shadow_rays
         if (STATS) add_stats(stats, 1u, hit, 0u, 0u, queued ? 0u : (uint32_t)L.total, queued ? Work{0u, 0u, 0u} : L.work);
         if (queued) { // staged in shared memory until the tile is complete, see flush()
             const uint32_t tid = threadIdx.x;
@@ -332,7 +344,8 @@ struct PrimaryPolicy {
             pix |= 0x80000000u;
         } else {
             const int x = (int)(pix & 32767u), y = (int)((pix >> 15) & 32767u);
-            emit_pixel<NORM>(f, ORTHO, bgra, steps_plane, pix, hit, pos, ncode, false, L.total, hit ? pos : (ORTHO ? f.fwd : primary_dir(x, y)));
+            if (QUEUED) emit_pixel<NORM, true>(f, ORTHO, bgra, steps_plane, pix, false, pos, 0u, false, L.total, ORTHO ? f.fwd : primary_dir(x, y));
+            else emit_pixel<NORM>(f, ORTHO, bgra, steps_plane, pix, hit, pos, ncode, false, L.total, hit ? pos : (ORTHO ? f.fwd : primary_dir(x, y)));
         }
         L.flags = ST_IDLE;
     }
@@ -355,8 +368,9 @@ __device__ __forceinline__ V3 sun_direction(const FrameParams& f, V3& once) {
 #define VX_SETUP_THREADS 256
 #define VX_SETUP_MIN_BLOCKS 4
 #endif
-template <int NORM, bool STATS>
-__global__ void __launch_bounds__(VX_SETUP_THREADS, VX_SETUP_MIN_BLOCKS) shadow_setup(WorldView w, FrameParams f, ShadowQueue q) {
+template <int NORM, bool STATS, bool F8>
+__global__ void __launch_bounds__(VX_SETUP_THREADS, VX_SETUP_MIN_BLOCKS) shadow_setup(WorldView w_in, FrameParams f, ShadowQueue q) {
+    const WorldView w = F8 ? factor8_view(w_in) : w_in;
     const unsigned long long n = *q.count;
     V3 sray;
     const V3 d = sun_direction<NORM>(f, sray);
@@ -513,22 +527,25 @@ __global__ void __launch_bounds__(256) bounce_setup(FrameParams f, ShadowQueue q
     }
 }
 
-template <int NORM, bool STATS, bool ORTHO>
-__global__ void __launch_bounds__(128, VX_MIN_BLOCKS) primary_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
+// SPEC: 8^3 bricks (F8 above) and the first launch of a shadowed frame (PrimaryPolicy's QUEUED).
+template <int NORM, bool STATS, bool ORTHO, bool SPEC>
+__global__ void __launch_bounds__(128, VX_MIN_BLOCKS) primary_rays(WorldView w_in, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
                                                                    unsigned long long* __restrict__ stats, ShadowQueue q, unsigned long long* next) {
     __shared__ float4 stage_rec[128];
     __shared__ uint32_t stage_aux[STATS ? 512 : 128];
     __shared__ uint32_t tile_slots[8];
     if (threadIdx.x < 8) tile_slots[threadIdx.x] = 0xFFFFFFFFu;
     __syncthreads();
-    PrimaryPolicy<NORM, STATS, ORTHO> pol(f, bgra, steps_plane, stats, q);
+    const WorldView w = SPEC ? factor8_view(w_in) : w_in;
+    PrimaryPolicy<NORM, STATS, ORTHO, SPEC> pol(f, bgra, steps_plane, stats, q);
     pol.stage_rec = stage_rec; pol.stage_aux = stage_aux; pol.tile_slot = tile_slots + 2 * (threadIdx.x >> 5);
     run_lanes<false, STATS>(w, pol, next);
 }
-template <int NORM, bool STATS, bool FUSE>
-__global__ void __launch_bounds__(128, VX_SHADOW_MIN_BLOCKS) shadow_rays(WorldView w, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
+template <int NORM, bool STATS, bool FUSE, bool F8>
+__global__ void __launch_bounds__(128, VX_SHADOW_MIN_BLOCKS) shadow_rays(WorldView w_in, FrameParams f, uint8_t* __restrict__ bgra, int32_t* __restrict__ steps_plane,
                                                                   ShadowQueue q, unsigned long long* next) {
     __shared__ uint2 shade_list[FUSE ? 4 * kShadeList : 1];
+    const WorldView w = F8 ? factor8_view(w_in) : w_in;
     ShadowPolicy<NORM, STATS, FUSE> pol(f, q, bgra, steps_plane, shade_list + (FUSE ? (threadIdx.x >> 5) * kShadeList : 0u));
     run_lanes<false, STATS>(w, pol, next);
 }
@@ -653,10 +670,11 @@ static int launch_trace(vx_tracer* t, const float* d_o, const float* d_d, size_t
     int rc = next_counter(t, s, &next);
     if (rc) return rc;
     unsigned blocks = 1;
-#define VX_LAUNCH(N, C) do { rc = persistent_blocks(t, trace_rays<N, C>, n, blocks); if (rc) return rc; \
-        trace_rays<N, C><<<blocks, 128, 0, s>>>(w, d_o, d_d, (unsigned long long)n, max_steps, p, next); } while (0)
-    if (count) { if (norm == 0) VX_LAUNCH(0, true); else if (norm == 1) VX_LAUNCH(1, true); else VX_LAUNCH(2, true); }
-    else { if (norm == 0) VX_LAUNCH(0, false); else if (norm == 1) VX_LAUNCH(1, false); else VX_LAUNCH(2, false); }
+#define VX_LAUNCH(N, C, F) do { rc = persistent_blocks(t, trace_rays<N, C, F>, n, blocks); if (rc) return rc; \
+        trace_rays<N, C, F><<<blocks, 128, 0, s>>>(w, d_o, d_d, (unsigned long long)n, max_steps, p, next); } while (0)
+    if (count) { if (norm == 0) VX_LAUNCH(0, true, false); else if (norm == 1) VX_LAUNCH(1, true, false); else VX_LAUNCH(2, true, false); }
+    else if (w.factor == 8) { if (norm == 0) VX_LAUNCH(0, false, true); else if (norm == 1) VX_LAUNCH(1, false, true); else VX_LAUNCH(2, false, true); }
+    else { if (norm == 0) VX_LAUNCH(0, false, false); else if (norm == 1) VX_LAUNCH(1, false, false); else VX_LAUNCH(2, false, false); }
 #undef VX_LAUNCH
     VX_CUDA(cudaGetLastError());
     return VX_OK;
@@ -913,6 +931,57 @@ extern "C" int vx_device_normalize(const float* dirs, float* out, size_t n, int 
     return VX_OK;
 }
 
+// The launches of one frame (see ShadowQueue above) on stream `cs`, shared by vx_render, vx_bounce_rays' primary pass and
+// vx_render_static.  `queue_pass`: the launch runs the sun-ray kernels too; `q` non-null means the primaries queue their hits.
+// Kernel variants: STATS when the caller counts; otherwise, for a world of 8^3 bricks, the kernels compiled for that factor
+// (and, for the primaries of a queued frame, without shading code).  Optional per-kernel timing (vx_tracer_set_timing):
+// events between the launches.
+template <int N, bool S, bool F8>
+static int launch_frame_as(vx_tracer* t, const WorldView& w, const FrameParams& f, void* d_bgra, int32_t* d_steps, unsigned long long* st,
+                           const ShadowQueue& q, unsigned long long* next1, unsigned long long* next2, bool sun_pass, bool fuse, cudaStream_t cs) {
+    int rc = VX_OK;
+    unsigned blocks = 1;
+    const unsigned dense_blocks = (unsigned)(t->sm_count > 0 ? t->sm_count : 148) * 8u; // grid-stride over a device-side count
+    const bool queued = q.count != nullptr; // shadows on, debug view off
+#define VX_MARK(i) do { if (t->timing) VX_CUDA(cudaEventRecord(t->ev[i], cs)); } while (0)
+#define VX_PRIMARY(ORTHO, SPEC) do { \
+        rc = persistent_blocks(t, primary_rays<N, S, ORTHO, SPEC>, f.ids, blocks); if (rc) return rc; \
+        VX_MARK(0); \
+        primary_rays<N, S, ORTHO, SPEC><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); } while (0)
+    t->timed_kernels = 0;
+    if (f.ortho_w > 0.0f) { if (F8 && queued) VX_PRIMARY(true, F8); else VX_PRIMARY(true, false); }
+    else { if (F8 && queued) VX_PRIMARY(false, F8); else VX_PRIMARY(false, false); }
+    VX_MARK(1); t->timed_kernels = 1;
+    if (sun_pass) {
+        shadow_setup<N, S, F8><<<dense_blocks * (256 / VX_SETUP_THREADS), VX_SETUP_THREADS, 0, cs>>>(w, f, q);
+        VX_MARK(2);
+        if (!S && fuse) {
+            rc = persistent_blocks(t, shadow_rays<N, false, true, F8>, f.ids, blocks); if (rc) return rc;
+            shadow_rays<N, false, true, F8><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, q, next2);
+            VX_MARK(3);
+        } else {
+            rc = persistent_blocks(t, shadow_rays<N, S, false, F8>, f.ids, blocks); if (rc) return rc;
+            shadow_rays<N, S, false, F8><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, q, next2);
+            VX_MARK(3);
+            shade_pixels<N, S><<<dense_blocks, 256, 0, cs>>>(f, (uint8_t*)d_bgra, d_steps, st, q);
+        }
+        VX_MARK(4); t->timed_kernels = 4;
+    }
+#undef VX_PRIMARY
+#undef VX_MARK
+    VX_CUDA(cudaGetLastError());
+    return VX_OK;
+}
+static int launch_frame(vx_tracer* t, const WorldView& w, const FrameParams& f, void* d_bgra, int32_t* d_steps, unsigned long long* st,
+                        const ShadowQueue& q, unsigned long long* next1, unsigned long long* next2, bool norm_host, bool sun_pass, bool fuse,
+                        cudaStream_t cs) {
+#define VX_GO(N, S, F8) return launch_frame_as<N, S, F8>(t, w, f, d_bgra, d_steps, st, q, next1, next2, sun_pass, fuse, cs)
+    const bool f8 = w.factor == 8;
+    if (norm_host) { if (st) VX_GO(1, true, false); else if (f8) VX_GO(1, false, true); else VX_GO(1, false, false); }
+    else { if (st) VX_GO(0, true, false); else if (f8) VX_GO(0, false, true); else VX_GO(0, false, false); }
+#undef VX_GO
+}
+
 static int fill_frame(vx_tracer* t, const vx_camera* cam, const vx_env* env, const vx_render_opts* o, uint32_t W, uint32_t H, FrameParams& f) {
     VX_REQUIRE(W > 0 && H > 0, "empty frame");
     VX_REQUIRE(W < 32768 && H < 32768, "frame dimensions must be below 32768");
@@ -1016,40 +1085,8 @@ extern "C" int vx_render(vx_tracer* t, const vx_camera* cam, const vx_env* env, 
     if (rc) return rc;
     if (shadow_pass) { rc = next_counter(t, cs, &next2); if (rc) return rc; }
     const bool fuse = t->fused_shade != 0; // vx_tracer_set_fused_shade: a frame in another GPU's memory is shaded inside the march
-    unsigned blocks = 1;
-    const unsigned dense_blocks = (unsigned)(t->sm_count > 0 ? t->sm_count : 148) * 8u; // grid-stride over a device-side count
-    // optional per-kernel timing (vx_tracer_set_timing): events between the launches, on the launching stream
-#define VX_MARK(i) do { if (t->timing) VX_CUDA(cudaEventRecord(t->ev[i], cs)); } while (0)
-    t->timed_kernels = 0;
-#define VX_LAUNCH(N, S) do { \
-        if (f.ortho_w > 0.0f) { \
-            rc = persistent_blocks(t, primary_rays<N, S, true>, f.ids, blocks); if (rc) return rc; \
-            VX_MARK(0); \
-            primary_rays<N, S, true><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); \
-        } else { \
-            rc = persistent_blocks(t, primary_rays<N, S, false>, f.ids, blocks); if (rc) return rc; \
-            VX_MARK(0); \
-            primary_rays<N, S, false><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, st, q, next1); \
-        } \
-        VX_MARK(1); t->timed_kernels = 1; \
-        if (shadow_pass && !t->primary_only) { \
-            shadow_setup<N, S><<<dense_blocks * (256 / VX_SETUP_THREADS), VX_SETUP_THREADS, 0, cs>>>(w, f, q); \
-            VX_MARK(2); \
-            if (!S && fuse) { \
-                rc = persistent_blocks(t, shadow_rays<N, false, true>, f.ids, blocks); if (rc) return rc; \
-                shadow_rays<N, false, true><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, q, next2); \
-                VX_MARK(3); \
-            } else { \
-                rc = persistent_blocks(t, shadow_rays<N, S, false>, f.ids, blocks); if (rc) return rc; \
-                shadow_rays<N, S, false><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, q, next2); \
-                VX_MARK(3); \
-                shade_pixels<N, S><<<dense_blocks, 256, 0, cs>>>(f, (uint8_t*)d_bgra, d_steps, st, q); \
-            } \
-            VX_MARK(4); t->timed_kernels = 4; } } while (0)
-    if (opts->norm_mode == VX_NORM_HOST) { if (st) VX_LAUNCH(1, true); else VX_LAUNCH(1, false); }
-    else { if (st) VX_LAUNCH(0, true); else VX_LAUNCH(0, false); }
-#undef VX_LAUNCH
-#undef VX_MARK
+    rc = launch_frame(t, w, f, d_bgra, d_steps, st, q, next1, next2, opts->norm_mode == VX_NORM_HOST, shadow_pass && !t->primary_only, fuse, cs);
+    if (rc) return rc;
     VX_CUDA(cudaGetLastError());
     return VX_OK;
 }
@@ -1138,24 +1175,8 @@ extern "C" int vx_render_static(const vx_world* world, const vx_camera* cam, con
         q.count = counters;
     }
     unsigned long long *next1 = counters + 8, *next2 = counters + 16;
-    unsigned blocks = 1;
-    const unsigned dense_blocks = (unsigned)(sd.sm_count > 0 ? sd.sm_count : 148) * 8u;
-#define VX_LAUNCH(N) do { \
-        if (f.ortho_w > 0.0f) { \
-            rc = persistent_blocks(&local, primary_rays<N, false, true>, f.ids, blocks); if (rc) return rc; \
-            primary_rays<N, false, true><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, nullptr, q, next1); \
-        } else { \
-            rc = persistent_blocks(&local, primary_rays<N, false, false>, f.ids, blocks); if (rc) return rc; \
-            primary_rays<N, false, false><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, nullptr, q, next1); \
-        } \
-        if (shadow_pass) { \
-            shadow_setup<N, false><<<dense_blocks * (256 / VX_SETUP_THREADS), VX_SETUP_THREADS, 0, cs>>>(w, f, q); \
-            rc = persistent_blocks(&local, shadow_rays<N, false, false>, f.ids, blocks); if (rc) return rc; \
-            shadow_rays<N, false, false><<<blocks, 128, 0, cs>>>(w, f, (uint8_t*)d_bgra, d_steps, q, next2); \
-            shade_pixels<N, false><<<dense_blocks, 256, 0, cs>>>(f, (uint8_t*)d_bgra, d_steps, nullptr, q); \
-        } } while (0)
-    if (opts->norm_mode == VX_NORM_HOST) VX_LAUNCH(1); else VX_LAUNCH(0);
-#undef VX_LAUNCH
+    rc = launch_frame(&local, w, f, d_bgra, d_steps, nullptr, q, next1, next2, opts->norm_mode == VX_NORM_HOST, shadow_pass, false, cs);
+    if (rc) return rc;
     VX_CUDA(cudaGetLastError());
     return VX_OK;
 }
