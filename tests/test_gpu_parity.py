@@ -430,3 +430,43 @@ def test_partitioned_build_equals_single_device_build(vx, case):
     with pytest.raises(vx.VxError):   # a pool that does not belong to these top-level bits is refused
         vx.World.from_parts(*dims, factor, top.data_ptr(), bounds.data_ptr(), pool.data_ptr(), occupied + 1, 0)
     r1.close(); r2.close(); whole.close(); parts.close()
+
+
+def test_chain_shortcuts_equal_the_ieee_operations(vx):
+    """The two shortcuts of the per-brick chain (vx_march.cuh): tmax_div(a, d) must be a / d for every float a and every
+    finite non-zero d (zero numerators are answered without the division), next_toward(x, down) must be
+    nextafterf(x, -+inf) for every float (VolumeRaytracer.cu:206-214, :457-459)."""
+    import ctypes as C
+    rng = np.random.default_rng(77)
+    special = np.array([0.0, -0.0, 1.0, -1.0, 8.0, 0.125, 1e-45, -1e-45, 1.1754944e-38, -1.1754944e-38, 5e-39, 3.4028235e38, -3.4028235e38,
+                        np.inf, -np.inf, np.nan, 1e-30, -1e-30, 1e30, 0.99999994, 1.0000001, 511.99997, 512.0], np.float32)
+    bits = rng.integers(0, 2**32, 200000, dtype=np.uint64).astype(np.uint32).view(np.float32)   # every exponent, NaNs and denormals included
+    near = (rng.uniform(-1030, 1030, 100000)).astype(np.float32)
+    a = np.concatenate([np.repeat(special, special.size), bits, near, np.zeros(1000, np.float32), -np.zeros(1000, np.float32)])
+    d = np.concatenate([np.tile(special, special.size), np.roll(bits, 1), rng.uniform(-1, 1, 100000).astype(np.float32),
+                        rng.uniform(-1, 1, 2000).astype(np.float32)])
+    ok = np.isfinite(d) & (d != 0)
+    d = np.where(ok, d, np.float32(0.57735026)).astype(np.float32)
+    n = a.size
+    out = np.zeros((6, n), np.float32)
+    L = vx.lib()
+    L.vx_debug_chain_math.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
+    vx._check(L.vx_debug_chain_math(a.ctypes.data, d.ctypes.data, n, out.ctypes.data, 0))
+    div, dev_div, up, down, dev_up, dev_down = out
+
+    def same(got, want, what):
+        nan = np.isnan(want)
+        assert np.array_equal(np.isnan(got), nan), what + ": NaNs differ"
+        bad = np.nonzero(~nan & (got.view(np.uint32) != want.view(np.uint32)))[0]
+        assert bad.size == 0, "%s: %d differ, first a=%r d=%r got=%r want=%r" % (what, bad.size, a[bad[0]], d[bad[0]], got[bad[0]], want[bad[0]])
+
+    # against the device's own operations (what the reference's kernels execute) ...
+    same(div, dev_div, "tmax_div vs div.rn")
+    same(up, dev_up, "next_toward(up) vs nextafterf")
+    same(down, dev_down, "next_toward(down) vs nextafterf")
+    # ... and against the host's (what the reference computes when its source runs on a CPU)
+    with np.errstate(all="ignore"):
+        same(div, (a / d).astype(np.float32), "tmax_div vs IEEE division")
+        same(up, np.nextafter(a, np.float32(np.inf)), "next_toward(up) vs libm")
+        same(down, np.nextafter(a, np.float32(-np.inf)), "next_toward(down) vs libm")
+    assert int((a == 0).sum()) > 2000 and int((np.abs(d) < 1.1754944e-38).sum()) > 50   # zero numerators and denormal divisors were in the sample

@@ -1356,6 +1356,37 @@ extern "C" int vx_debug_fine_stats(unsigned long long out[8], int device) {
 
 // diagnostics (VX_TILE_TRACE=1): for every 8x4 tile of the last vx_render, the SM cycles it kept its warp and the low word of
 // %globaltimer (ns) at which the warp drew it; out arrays hold `capacity` entries, *n = tiles of that launch
+// Diagnostics (not in vxrt.h): the march's two exactness-critical shortcuts evaluated on the device for host arrays, so a test
+// can put them beside the operations they stand for — tmax_div(a, d) against a / d, next_toward(x, down) against
+// nextafterf(x, -+inf).  out: 6 planes of n floats — tmax_div(a, d), __fdiv_rn(a, d), next_toward(a, up), next_toward(a, down),
+// nextafterf(a, +inf), nextafterf(a, -inf).
+__global__ void chain_math_kernel(const float* __restrict__ a, const float* __restrict__ d, size_t n, float* __restrict__ out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = vx::tmax_div(a[i], d[i]);
+    out[n + i] = __fdiv_rn(a[i], d[i]);
+    out[2 * n + i] = vx::next_toward(a[i], false);
+    out[3 * n + i] = vx::next_toward(a[i], true);
+    out[4 * n + i] = nextafterf(a[i], CUDART_INF_F);
+    out[5 * n + i] = nextafterf(a[i], -CUDART_INF_F);
+}
+extern "C" int vx_debug_chain_math(const float* a, const float* d, size_t n, float* out, int device) {
+    VX_REQUIRE(a && d && out, "NULL argument");
+    if (!n) return VX_OK;
+    DeviceGuard guard(device);
+    float* buf = nullptr;
+    VX_CUDA(cudaMalloc(&buf, n * 32));
+    cudaError_t e = cudaMemcpy(buf, a, n * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(buf + n, d, n * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        chain_math_kernel<<<(unsigned)((n + 255) / 256), 256>>>(buf, buf + n, n, buf + 2 * n);
+        e = cudaMemcpy(out, buf + 2 * n, n * 24, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(buf);
+    VX_CUDA(e);
+    return VX_OK;
+}
+
 extern "C" int vx_debug_tile_trace(vx_tracer* t, uint32_t* out_cycles, uint32_t* out_start_ns, size_t capacity, size_t* n) {
     VX_REQUIRE(t && n, "NULL argument");
     *n = 0;
