@@ -266,7 +266,7 @@ def run_reference(args, wl, wl_name):
             "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -284,8 +284,6 @@ class Bench:
         if not torch.cuda.is_available():
             raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback")
         torch.cuda.set_device(self.dev)
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"   # NCCL's version banner goes to stdout, where exactly one JSON line belongs
         if self.world_size > 1:
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.dev))
         self.stream = torch.cuda.current_stream().cuda_stream
@@ -660,7 +658,7 @@ def run_ours(args, wl, wl_name):
                 print(json.dumps({"parity": line["parity"]}), file=sys.stderr)
                 raise SystemExit("bench: the timed frame does not match the CPU oracle (see parity above); no value printed")
         line["gpu_launches"] = B.launches
-        print(json.dumps(line), flush=True)
+        emit(line)
         return
 
     # ---------------- N > 1 ----------------
@@ -936,11 +934,34 @@ def run_ours(args, wl, wl_name):
                                           "barriers, max over ranks); identical = same top-level bits, counters, 8192 sampled bricks and the same 4K frame"}},
             "gpu_launches": B.launches, "wall_s_timed_region": wall,
         })
-        print(json.dumps(line), flush=True)
+        emit(line)
     dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line.  Libraries write there too (NCCL prints its version banner to stdout at NCCL_DEBUG=WARN
+    as well as =VERSION, from every rank, and all ranks share torchrun's stdout), so file descriptor 1 is pointed at stderr for
+    the whole run and the line is written to the original descriptor by emit()."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)

@@ -62,3 +62,18 @@ def test_no_cpu_fallback_without_device(vx):
         pytest.skip("a GPU is present")
     with pytest.raises(vx.VxError):
         vx.World.from_noise(64, 64, 64, 8)
+
+
+def test_bench_stdout_is_one_json_line_whatever_libraries_print():
+    """bench.py's contract is ONE JSON line on stdout; NCCL writes its version banner to file descriptor 1 from every rank
+    (at NCCL_DEBUG=WARN too).  bench.claim_stdout() points fd 1 at stderr and emit() writes to the original descriptor."""
+    import json
+    import subprocess
+    import sys
+    code = ("import os, sys; sys.argv = ['bench.py']; import bench; bench.claim_stdout(); os.write(1, b'NCCL version 2.28.9+cuda12.9\\n'); "
+            "print('a library print'); bench.emit({'metric': 'Mrays/s', 'value': 1.0})")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=ROOT)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.splitlines()
+    assert len(lines) == 1 and json.loads(lines[0])["value"] == 1.0
+    assert "NCCL version" in r.stderr and "a library print" in r.stderr
