@@ -18,7 +18,7 @@
 #define VX_TILE_SHAPE 0 // pixels a warp of primary_rays takes at a time: 0 = 8x4, 1 = 16x2, 2 = 32x1
 #endif
 #ifndef VX_TRACE_MIN_BLOCKS
-#define VX_TRACE_MIN_BLOCKS 8 // same for the batch kernel (it carries the parity planes' counters too)
+#define VX_TRACE_MIN_BLOCKS 10 // the batch kernel: 10 since round 2 (bounce rays 2.11 -> 2.05 ms; 8: 2.11, 9: 2.10, 11: 2.07, 12: 2.08)
 #endif
 #ifndef VX_SHADOW_MIN_BLOCKS
 #define VX_SHADOW_MIN_BLOCKS 10 // sun rays: 10 since the chain trims of round 2 (0.840 -> 0.825 ms; 11, 12: the same with spills; round 1: 9)
