@@ -435,7 +435,7 @@ def test_partitioned_build_equals_single_device_build(vx, case):
 def test_chain_shortcuts_equal_the_ieee_operations(vx):
     """The two shortcuts of the per-brick chain (vx_march.cuh): tmax_div(a, d) must be a / d for every float a and every
     finite non-zero d (zero numerators are answered without the division), next_toward(x, down) must be
-    nextafterf(x, -+inf) for every float (VolumeRaytracer.cu:206-214, :457-459)."""
+    nextafterf(x, -+inf) for every float (VolumeRaytracer.cu:203-205, :452-460)."""
     import ctypes as C
     rng = np.random.default_rng(77)
     special = np.array([0.0, -0.0, 1.0, -1.0, 8.0, 0.125, 1e-45, -1e-45, 1.1754944e-38, -1.1754944e-38, 5e-39, 3.4028235e38, -3.4028235e38,

@@ -108,7 +108,7 @@ __device__ __forceinline__ V3 to_brick_units(const WorldView& w, V3 p) {
     return mk(fdiv(p.x, ff), fdiv(p.y, ff), fdiv(p.z, ff));
 }
 
-// tMax = (face - s) / d (VolumeRaytracer.cu:206-214) for a direction component that is finite and not zero (F_DNZ).
+// tMax = (face - s) / d (VolumeRaytracer.cu:203-205) for a direction component that is finite and not zero (F_DNZ).
 // A zero numerator — the start lies exactly on the face it is measured to: every brick entered through an upper face of
 // its tight box by a ray that descends along that axis, every camera on an integer brick coordinate — gives (+-0) / d, a
 // zero with the XOR of the signs.  div.rn's in-line path does not take zero operands (FCHK sends them through a
@@ -121,7 +121,7 @@ __device__ __forceinline__ float tmax_div(float a, float d) {
 }
 __device__ __forceinline__ bool finite_nonzero(float v) { return (__float_as_uint(v) & 0x7FFFFFFFu) - 1u < 0x7F7FFFFFu; }
 
-// nextafterf(x, down ? -inf : +inf) (the nudge of VolumeRaytracer.cu:457-459).  For a finite x that is neither zero nor
+// nextafterf(x, down ? -inf : +inf) (the nudge of VolumeRaytracer.cu:452-460).  For a finite x that is neither zero nor
 // the largest float it is one step on the bit pattern, away from zero or towards it; everything else goes to the library.
 __device__ __forceinline__ float next_toward(float x, bool down) {
 #if VX_OPT_NEXT
