@@ -239,7 +239,8 @@ __device__ __forceinline__ void fast_step(float& tx, float& ty, float& tz, uint3
 // primaries 4 steps, 1/4: 1.41 ms; 8 steps: 1.37 (1/4 and 1/2 alike); sun rays 4 steps, 1/4: 1.00 ms; 4 steps, 1/2: 0.95-0.96;
 // incoherent bounce rays (batch kernel) 4 steps, 1/4: 2.30 ms; 8 steps: 2.25; 1/2: 2.46.
 #ifndef VX_PRIMARY_QUAD
-#define VX_PRIMARY_QUAD 8
+#define VX_PRIMARY_QUAD 4 // round 2, after the chain trims: 4 steps 1.280 / 0.594 / 0.527 ms (overview / grazing / diagonal camera), 8 steps
+                          // 1.283 / 0.610 / 0.545, 2 steps 1.321 / 0.593 / 0.525 (profiles/r02_sweep_fast_loop_schedule_after_trims.log)
 #endif
 #ifndef VX_PRIMARY_LEAVE_NUM
 #define VX_PRIMARY_LEAVE_NUM 1
